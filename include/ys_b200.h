@@ -1,0 +1,159 @@
+/* ys_b200.h -- C ABI of the B200-native detection-head hot path.
+ *
+ * One shared library (yolo_scratch_b200/libys_b200.so, built by
+ * yolo_scratch_b200/build.py with nvcc -gencode arch=compute_100a,code=sm_100a).
+ * The reference (Pratye/yolo-scratch, yolo_scratch_cuda) is pure Python and has no
+ * FFI; every entry point below names the reference function(s) it replaces
+ * (paths relative to /root/reference/yolo_scratch_cuda/).  INTEGRATION.md shows the
+ * ctypes binding a maintainer would add.
+ *
+ * Conventions
+ *  - All tensor pointers are DEVICE pointers unless the parameter name ends in
+ *    _host.  Plain pointers + sizes only; no torch types.
+ *  - No allocation, no host synchronisation, no global state: scratch lives in a
+ *    caller-provided workspace (size from ys_*_workspace_bytes), the last
+ *    argument is the cudaStream_t to launch on (as void*).
+ *  - Return 0 on success; YS_ERR_* (<0) for bad arguments; a positive value is a
+ *    cudaError_t from a launch.  ys_last_error() gives a thread-local message.
+ *  - Never throws across the ABI.  Re-entrant across streams as long as each
+ *    in-flight call has its own workspace.
+ */
+#ifndef YS_B200_H
+#define YS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YS_OK 0
+#define YS_ERR_BAD_ARG (-1)
+#define YS_ERR_WORKSPACE (-2)
+#define YS_ERR_UNSUPPORTED (-3)
+
+#define YS_MAX_LEVELS 8
+
+/* Library identity. */
+int ys_version(void);
+const char *ys_last_error(void);
+/* SM count / arch the library was built for and sees at run time (host-side query;
+ * returns 0 and fills the ints, or a cudaError_t). */
+int ys_device_info(int *sm_count, int *cc_major, int *cc_minor);
+
+/* ---------------------------------------------------------------------------
+ * Fused detection loss: assign + BCE + CIoU + DFL, forward AND backward.
+ * Replaces v8DetectionLoss.__call__ (losses/yolo_v8_loss.py:372-499) including
+ * preprocess (:501-527), make_anchors (:541-552), bbox_decode (:529-538),
+ * TaskAlignedAssigner.forward (:78-180) and BboxLoss.forward (:280-324), plus
+ * the autograd backward of all of it (train_yolo11_cuda.py:57 loss.backward()).
+ *
+ *  level_x_host[n_levels]    device pointers to the NCHW head outputs (B, 4*reg_max+nc, h, w), fp32, contiguous
+ *  level_grad_host[n_levels] device pointers to same-shaped gradient buffers, or NULL => forward only
+ *  level_h/w/stride_host     per-level sizes and strides (host arrays)
+ *  batch_idx (N) i64, cls (N) i64, bboxes (N,4) fp32 normalised xyxy: the flat GT list of the batch dict
+ *                            (datasets/crater_dataset_cuda.py:336-341); any order; rows with batch_idx
+ *                            outside [0,B) are ignored as the reference's mask does (:519)
+ *  scale_x, scale_y          pixel scale applied to (x1,x2) and (y1,y2): the reference uses
+ *                            imgsz = feats[0].shape[2:]*stride[0] and scales x by imgsz[0], y by imgsz[1] (:400,:515)
+ *  hyp_box/cls/dfl           7.5 / 0.5 / 1.5 (:368-370); alpha/beta 0.5 / 4.0 (:363)
+ *  loss_out[4]               device: [loss.sum()*B, box*hyp, cls*hyp, dfl*hyp]  (:495-499)
+ *  Gradients are d(loss.sum()*B)/d(level_x) (i.e. upstream grad 1.0).
+ *  Optional exports (may be NULL): pred_boxes_px (B,A,4) decoded boxes in pixels (:412),
+ *  target_gt_idx (B,A) i32 (-1 = background), norm (B,A) the per-anchor target score (:173-178).
+ *  stages: 0 or YS_STAGE_ALL runs the whole path; a subset re-runs only those kernels on the state a
+ *  previous full call left in the SAME workspace (bench.py times the dominant kernel alone this way).
+ */
+#define YS_STAGE_PACK 1   /* k_pack_gt        flat GT list -> per-image CSR, pixel boxes */
+#define YS_STAGE_SCAN 2   /* k_assign_scan    decode + pairwise IoU / in-box + preliminary assignment */
+#define YS_STAGE_FIXUP 4  /* k_assign_fixup   forced assignments + target_scores_sum */
+#define YS_STAGE_LOSS 8   /* k_loss_fwd_bwd   BCE + CIoU + DFL forward and backward */
+#define YS_STAGE_FINAL 16 /* k_loss_finalize  ordered reduction of the partial sums */
+#define YS_STAGE_ALL 31
+size_t ys_detection_loss_workspace_bytes(int B, int A, int n_gt);
+int ys_detection_loss(int n_levels, const float *const *level_x_host, float *const *level_grad_host,
+                      const int *level_h_host, const int *level_w_host, const float *level_stride_host,
+                      int B, int nc, int reg_max,
+                      const int64_t *batch_idx, const int64_t *cls, const float *bboxes, int n_gt,
+                      float scale_x, float scale_y,
+                      float hyp_box, float hyp_cls, float hyp_dfl, float alpha, float beta,
+                      float *loss_out,
+                      float *pred_boxes_px, int32_t *target_gt_idx, float *norm, int stages,
+                      void *workspace, size_t workspace_bytes, void *stream);
+
+/* In-place `grad *= *scale` unless *scale == 1.0f (device scalar; no host sync).
+ * Used by the autograd wrapper when the upstream gradient is not 1. */
+int ys_scale_inplace(float *data, size_t n, const float *scale_dev, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * TaskAlignedAssigner.forward on dense inputs (losses/yolo_v8_loss.py:78-180,
+ * helpers :182-270).  Shapes as the reference: pd_scores (B,A,nc) probabilities,
+ * pd_bboxes (B,A,4) px xyxy, anc_points (A,2) px, gt_labels (B,G) f32,
+ * gt_bboxes (B,G,4), mask_gt (B,G) f32.  Outputs: target_labels (B,A) f32,
+ * target_bboxes (B,A,4), target_scores (B,A,nc) (may be NULL), fg_mask (B,A) u8,
+ * target_gt_idx (B,A) i64, norm (B,A) f32 (may be NULL).  G must be > 0 (the G==0 return of
+ * :100-108 is produced by the Python shim without a launch).
+ */
+size_t ys_assign_workspace_bytes(int B, int A, int G);
+int ys_assign(int B, int A, int G, int nc,
+              const float *pd_scores, const float *pd_bboxes, const float *anc_points,
+              const float *gt_labels, const float *gt_bboxes, const float *mask_gt,
+              float alpha, float beta, float eps,
+              float *target_labels, float *target_bboxes, float *target_scores,
+              uint8_t *fg_mask, int64_t *target_gt_idx, float *norm,
+              void *workspace, size_t workspace_bytes, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * Inference decode: DFL.forward + Detect.inference + dist2bbox(xywh=True, dim=1)
+ * (models/yolo11_modules.py:180-192, :248-266, :303-312).
+ * out: (B, 4+nc, A) channels-first [cx,cy,w,h]*stride, sigmoid(cls)  (layout 0)
+ *   or (B, A, 4+nc) anchor-major, the layout decode_predictions_for_metrics documents (layout 1).
+ */
+int ys_decode_infer(int n_levels, const float *const *level_x_host, const int *level_h_host,
+                    const int *level_w_host, const float *level_stride_host, int B, int nc, int reg_max,
+                    float *out, int layout, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * Batched NMS: decode_predictions_for_metrics + nms_simple + calculate_iou_batch_simple
+ * (train_yolo11_cuda.py:265-358, :361-399, :402-437).
+ *  pred     (B, A, 4+nc) if layout==1, (B, 4+nc, A) if layout==0; xywh px + class probabilities
+ *  per image: best class (first max), score > conf, xywh->xyxy, greedy NMS in score-descending
+ *  order (ties: lower anchor index first), suppress when IoU > iou_thr; class_aware != 0 restricts
+ *  suppression to same-class pairs (non-default).
+ *  Outputs, each with row stride A per image, first keep_count[b] rows valid, score-descending:
+ *   keep_anchor (B,A) i32 source anchor index, keep_boxes (B,A,4) = clamp(xyxy/img_size,0,1),
+ *   keep_scores (B,A), keep_labels (B,A) i32, keep_count (B) i32.
+ */
+size_t ys_nms_workspace_bytes(int B, int A);
+int ys_nms_batched(const float *pred, int layout, int B, int A, int nc,
+                   float conf_thr, float iou_thr, float img_size, int class_aware,
+                   int32_t *keep_anchor, float *keep_boxes, float *keep_scores, int32_t *keep_labels,
+                   int32_t *keep_count, void *workspace, size_t workspace_bytes, void *stream);
+
+/* nms_simple on one already-filtered set (train_yolo11_cuda.py:361-399): boxes (N,4) xyxy, scores (N).
+ * labels may be NULL (class-agnostic).  keep (N) i32 receives indices into the input, score-descending;
+ * keep_count (1) i32. */
+int ys_nms_single(const float *boxes, const float *scores, const int32_t *labels, int N, float iou_thr,
+                  int32_t *keep, int32_t *keep_count, void *workspace, size_t workspace_bytes, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * Pairwise IoU matrices.
+ *  kind 0: utils.metrics.calculate_iou_batch / calculate_iou_batch_simple
+ *          (utils/metrics.py:49-81, train_yolo11_cuda.py:402-437): inter/(a1+a2-inter+1e-6)
+ *  kind 1: bbox_iou(xywh=False) broadcast form used by the assigner (losses/yolo_v8_loss.py:31-44)
+ *  boxes1 (N,4), boxes2 (M,4) -> out (N,M)
+ */
+int ys_pairwise_iou(const float *boxes1, int N, const float *boxes2, int M, int kind, float *out, void *stream);
+
+/* Elementwise bbox_iou on paired boxes (losses/yolo_v8_loss.py:12-61): box1,box2 (n,4) -> out (n).
+ * mode 0 IoU, 1 GIoU, 2 DIoU, 3 CIoU; xywh != 0 => inputs are cx,cy,w,h.
+ * If grad_box1 != NULL also writes d(sum_i out_i * gout_i)/d box1 (n,4) (alpha constant, :54-55);
+ * gout may be NULL (= ones). */
+int ys_bbox_iou(const float *box1, const float *box2, int n, int xywh, int mode, float eps, float *out,
+                const float *gout, float *grad_box1, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YS_B200_H */

@@ -1,0 +1,188 @@
+"""GPU parity: fused detection loss (ys_detection_loss through the drop-in v8DetectionLoss) vs the reference
+fixtures and the oracle port.  Loss items / total / gradients within 1e-5 relative (gradients relative to the
+gradient's max-norm); assignment indices bit-exact through the spliced-oracle test (§4.2)."""
+import pytest
+import torch
+
+from conftest import load_golden, golden_names, t, digest_close
+from yolo_scratch_b200 import synth
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+
+
+class Detect(torch.nn.Module):
+    def __init__(self, nc, reg_max=16, strides=synth.LEVEL_STRIDES):
+        super().__init__()
+        self.nc, self.reg_max = nc, reg_max
+        self.stride = torch.tensor([float(s) for s in strides])
+        self.p = torch.nn.Parameter(torch.zeros(1))
+
+
+def make_criterion(nc):
+    from yolo_scratch_b200.losses import v8DetectionLoss
+    return v8DetectionLoss(Detect(nc).cuda())
+
+
+def run_cuda(feats, batch, nc, export=False):
+    crit = make_criterion(nc)
+    crit.export_assignment = export
+    leaves = [f.cuda().requires_grad_(True) for f in feats]
+    total, items = crit(leaves, {k: v.cuda() for k, v in batch.items()})
+    total.backward()
+    torch.cuda.synchronize()
+    return total.detach().cpu(), items.cpu(), [l.grad.cpu() for l in leaves], crit
+
+
+def assert_grads_close(got, ref, rtol=RTOL):
+    for i, (a, b) in enumerate(zip(got, ref)):
+        scale = b.abs().max().item() or 1.0
+        err = (a - b).abs().max().item() / scale
+        assert err <= rtol, f"level {i}: grad err {err:.3e} (rel. to max-norm {scale:.3e})"
+
+
+@pytest.mark.parametrize("name", golden_names("loss_small"))
+def test_loss_golden_small(cuda_lib, name):
+    g = load_golden(name)
+    feats = [t(g["f0"]), t(g["f1"]), t(g["f2"])]
+    batch = {"batch_idx": t(g["batch_idx"]), "cls": t(g["cls"]), "bboxes": t(g["bboxes"])}
+    total, items, grads, _ = run_cuda(feats, batch, int(g["nc"]))
+    assert items.dtype == torch.float32 and items.shape == (3,)
+    assert torch.allclose(items, t(g["items"]), rtol=RTOL, atol=1e-7), (items, g["items"])
+    assert torch.allclose(total, t(g["total"]), rtol=RTOL)
+    assert_grads_close(grads, [t(g["g0"]), t(g["g1"]), t(g["g2"])])
+
+
+@pytest.mark.parametrize("name", golden_names("loss_c1"))
+def test_loss_golden_c1(cuda_lib, name):
+    """BASELINE.json configs[0]: B=2, 640 px, nc=80, <=20 GT/img -- against the reference's own outputs."""
+    g = load_golden(name)
+    seed = int(g["seed"])
+    feats = synth.make_head_levels(2, 640, 80, 16, seed=seed)
+    batch = synth.make_gt_batch(2, 80, 20, seed=seed + 1, p_empty=0.0)
+    total, items, grads, _ = run_cuda(feats, batch, 80)
+    assert torch.allclose(items, t(g["items"]), rtol=RTOL), (items, g["items"])
+    assert torch.allclose(total, t(g["total"]), rtol=RTOL)
+    for gr, key in zip(grads, ("g0", "g1", "g2")):
+        digest_close(gr, g, key, RTOL)
+
+
+@pytest.mark.parametrize("seed,B,max_gt,kw", [
+    (200, 4, 20, {}),
+    (201, 8, 20, {"p_tiny": 0.3, "p_nested": 0.3}),
+    (202, 3, 40, {"p_empty": 0.34, "p_nested": 0.3}),
+])
+def test_loss_vs_oracle_640_with_spliced_assignment(cuda_lib, seed, B, max_gt, kw):
+    from oracle import ref_port as orc
+    feats = synth.make_head_levels(B, 640, 80, 16, seed=seed)
+    batch = synth.make_gt_batch(B, 80, max_gt, seed=seed + 1, **kw)
+    total, items, grads, crit = run_cuda(feats, batch, 80, export=True)
+    leaves = [f.clone().requires_grad_(True) for f in feats]
+    rtotal, ritems, parts = orc.detection_loss(leaves, batch, 80, 16, synth.LEVEL_STRIDES, return_parts=True)
+    rtotal.backward()
+    ex = {k: v.cpu() for k, v in crit.last_export.items()}
+    # (1) decoded boxes to 1e-6 of the image size
+    assert (ex["pred_bboxes_px"] - parts["pred_bboxes_px"]).abs().max().item() <= 1e-6 * 640 * 4
+    # (2) spliced oracle: the oracle assigner fed with OUR decoded boxes must give OUR indices bit-exactly
+    A = ex["pred_bboxes_px"].shape[1]
+    imgsz = torch.tensor([640.0, 640.0])
+    tg = orc.pack_targets(batch["cls"], batch["bboxes"], batch["batch_idx"], B, imgsz)
+    anc, st = orc.anchors_for([f.shape[2:] for f in feats], synth.LEVEL_STRIDES)
+    flat = torch.cat([f.view(B, 144, -1) for f in feats], 2)
+    scores = flat[:, 64:].permute(0, 2, 1).sigmoid()
+    if tg.shape[1] > 0:
+        _, _, _, fg, tgi = orc.assign(scores, ex["pred_bboxes_px"], anc * st, tg[..., 0], tg[..., 1:5],
+                                      (tg[..., 5] > 0).float(), 80)
+        ours_fg = ex["target_gt_idx"] >= 0
+        assert torch.equal(ours_fg, fg.bool())
+        assert torch.equal(ex["target_gt_idx"].clamp(min=0).long(), tgi)
+    # (3) loss and gradients
+    assert torch.allclose(items, ritems, rtol=RTOL, atol=1e-7), (items, ritems)
+    assert torch.allclose(total, rtotal.detach(), rtol=RTOL)
+    assert_grads_close(grads, [l.grad for l in leaves])
+
+
+def test_loss_forward_only_and_tuple_input(cuda_lib):
+    """validate(): criterion((y, x), batch) under no_grad takes preds[1] (reference :387-389) and skips the backward."""
+    from oracle import ref_port as orc
+    feats = synth.make_head_levels(2, 128, 8, 16, seed=210)
+    batch = synth.make_gt_batch(2, 8, 5, seed=211, imgsz=128, p_empty=0.0)
+    crit = make_criterion(8)
+    with torch.no_grad():
+        total, items = crit((torch.zeros(1).cuda(), [f.cuda() for f in feats]), {k: v.cuda() for k, v in batch.items()})
+    rtotal, ritems = orc.detection_loss(feats, batch, 8, 16, synth.LEVEL_STRIDES)
+    assert not total.requires_grad
+    assert torch.allclose(items.cpu(), ritems, rtol=RTOL, atol=1e-7)
+
+
+def test_loss_upstream_gradient_scaling_and_unsorted_targets(cuda_lib):
+    """(loss * 0.25).backward() scales the stored gradients on the device; shuffled GT rows give the same result
+    when per-image order is preserved (the reference's mask-based gather is order-preserving per image)."""
+    feats = synth.make_head_levels(3, 128, 8, 16, seed=220)
+    batch = synth.make_gt_batch(3, 8, 6, seed=221, imgsz=128, p_empty=0.0)
+    _, items, grads, _ = run_cuda(feats, batch, 8)
+    crit = make_criterion(8)
+    leaves = [f.cuda().requires_grad_(True) for f in feats]
+    # interleave the images' rows round-robin: batch_idx becomes unsorted, within-image order is kept
+    per_img = [(batch["batch_idx"] == b).nonzero().squeeze(1).tolist() for b in range(3)]
+    perm = []
+    while any(per_img):
+        for lst in per_img:
+            if lst:
+                perm.append(lst.pop(0))
+    perm = torch.tensor(perm)
+    sh = {k: v[perm].cuda() for k, v in batch.items()}
+    assert not torch.equal(sh["batch_idx"].cpu(), batch["batch_idx"])
+    total, items2 = crit(leaves, sh)
+    (total * 0.25).backward()
+    torch.cuda.synchronize()
+    assert torch.allclose(items2.cpu(), items, rtol=1e-6)
+    for a, b in zip(leaves, grads):
+        assert torch.allclose(a.grad.cpu(), b * 0.25, rtol=1e-6, atol=1e-12)
+    # rows with batch_idx outside [0, B) are ignored, as the reference's `batch_idx == i` masks do
+    junk = {"batch_idx": torch.cat((sh["batch_idx"], torch.tensor([7, -1]).cuda())),
+            "cls": torch.cat((sh["cls"], torch.zeros(2, 1, dtype=torch.long).cuda())),
+            "bboxes": torch.cat((sh["bboxes"], torch.rand(2, 4).cuda()))}
+    with torch.no_grad():
+        _, items3 = crit([f.cuda() for f in feats], junk)
+    assert torch.allclose(items3.cpu(), items, rtol=1e-6)
+
+
+def test_loss_full_config2_properties(cuda_lib):
+    """BASELINE.json configs[1] shape (B=64, 640 px): size-independent properties -- shard additivity (the path is
+    per-image independent): unnormalised per-shard sums recombine to the full-batch loss; zero box
+    gradients on background anchors; finite everything."""
+    B = 64
+    feats = synth.make_head_levels(B, 640, 80, 16, seed=230)
+    batch = synth.make_gt_batch(B, 80, 20, seed=231)
+    crit = make_criterion(80)
+    crit.export_assignment = True
+    leaves = [f.cuda().requires_grad_(True) for f in feats]
+    total, items = crit(leaves, {k: v.cuda() for k, v in batch.items()})
+    total.backward()
+    ex = crit.last_export
+    fg = ex["target_gt_idx"] >= 0
+    tss = max(ex["norm"].double().sum().item(), 1.0)
+    assert torch.isfinite(items).all() and all(torch.isfinite(l.grad).all() for l in leaves)
+    # background anchors get exactly zero gradient on the 64 box channels
+    off = 0
+    for l in leaves:
+        hw = l.shape[2] * l.shape[3]
+        bg = ~fg[:, off:off + hw]
+        gbox = l.grad[:, :64].reshape(B, 64, hw)
+        assert (gbox.abs().amax(1)[bg] == 0).all()
+        off += hw
+    # shards of 16 images: sum_s items_s * tss_s == items * tss
+    acc = torch.zeros(3, dtype=torch.float64)
+    for s in range(4):
+        sel = (batch["batch_idx"] >= 16 * s) & (batch["batch_idx"] < 16 * (s + 1))
+        sb = {"batch_idx": (batch["batch_idx"][sel] - 16 * s).cuda(), "cls": batch["cls"][sel].cuda(),
+              "bboxes": batch["bboxes"][sel].cuda()}
+        c2 = make_criterion(80)
+        c2.export_assignment = True
+        with torch.no_grad():
+            _, it = c2([f[16 * s:16 * (s + 1)].cuda() for f in feats], sb)
+        tss_s = max(c2.last_export["norm"].double().sum().item(), 1.0)
+        assert torch.equal(c2.last_export["target_gt_idx"], ex["target_gt_idx"][16 * s:16 * (s + 1)])
+        acc += it.double().cpu() * tss_s
+    assert torch.allclose(acc / tss, items.double().cpu(), rtol=1e-5)

@@ -1,0 +1,131 @@
+"""GPU parity: batched NMS / decode-for-metrics / nms_simple vs the reference fixtures and the C oracle.
+Keep lists bit-exact; kept boxes / scores / labels bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, golden_names, t, digest_close
+from yolo_scratch_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _pred_of(g):
+    B, A, nc = int(g["B"]), int(g["A"]), int(g["nc"])
+    if "pred" in g:
+        return t(g["pred"])
+    pred = synth.make_nms_predictions(B, A, nc, 640, seed=int(g["seed"]), clustered=bool(g["clustered"]))
+    digest_close(pred, g, "in_digest", 0.0)
+    return pred
+
+
+@pytest.mark.parametrize("name", golden_names("nms_"))
+def test_decode_for_metrics_golden(cuda_lib, name):
+    from yolo_scratch_b200.train_yolo11_cuda import decode_predictions_for_metrics, nms_batched
+    g = load_golden(name)
+    pred = _pred_of(g).cuda()
+    conf, thr = float(g["conf"]), float(g["iou"])
+    res = decode_predictions_for_metrics(pred, 640, conf, thr, pred.device)
+    ka, _, _, _, kc = nms_batched(pred, conf, thr, 640)
+    for b in range(int(g["B"])):
+        k = int(kc[b])
+        assert np.array_equal(ka[b, :k].cpu().numpy(), g[f"keep{b}"]), f"keep list differs (image {b})"
+        assert torch.equal(res[b]["boxes"].cpu(), t(g[f"boxes{b}"]))
+        assert torch.equal(res[b]["scores"].cpu(), t(g[f"scores{b}"]))
+        assert torch.equal(res[b]["labels"].cpu().int(), t(g[f"labels{b}"]))
+        assert res[b]["labels"].dtype == torch.int64
+
+
+@pytest.mark.parametrize("clustered", [False, True])
+@pytest.mark.parametrize("layout", [1, 0])
+def test_nms_config4_shape_vs_c_oracle(cuda_lib, clustered, layout):
+    """BASELINE.json configs[3] shape per image (8400 candidates x 80 classes, conf 0.001 / IoU 0.7), 6 images."""
+    from oracle import c_oracle
+    from yolo_scratch_b200.train_yolo11_cuda import nms_batched
+    B = 6
+    pred = synth.make_nms_predictions(B, 8400, 80, 640, seed=300 + int(clustered), clustered=clustered)
+    dev = pred.cuda() if layout == 1 else pred.permute(0, 2, 1).contiguous().cuda()
+    ka, kb, ks, kl, kc = nms_batched(dev, 0.001, 0.7, 640, layout=layout)
+    for b in range(B):
+        xyxy, sc, cl, src = c_oracle.filter_candidates(pred[b], 0.001)
+        keep = c_oracle.nms(xyxy, sc, 0.7)
+        k = int(kc[b])
+        assert k == len(keep)
+        assert np.array_equal(ka[b, :k].cpu().numpy(), src[keep])
+        assert np.array_equal(kl[b, :k].cpu().numpy(), cl[keep])
+        assert np.array_equal(ks[b, :k].cpu().numpy(), sc[keep])
+        assert np.array_equal(kb[b, :k].cpu().numpy(), np.clip(xyxy[keep] / np.float32(640), 0, 1))
+        s = ks[b, :k]
+        assert (s[1:] <= s[:-1]).all()      # score-sorted
+
+
+def test_nms_class_aware_vs_oracle(cuda_lib):
+    from oracle import c_oracle
+    from yolo_scratch_b200.train_yolo11_cuda import nms_batched
+    pred = synth.make_nms_predictions(3, 3000, 6, 640, seed=310, clustered=True)
+    ka, _, _, _, kc = nms_batched(pred.cuda(), 0.01, 0.5, 640, class_aware=True)
+    for b in range(3):
+        xyxy, sc, cl, src = c_oracle.filter_candidates(pred[b], 0.01)
+        keep = c_oracle.nms(xyxy, sc, 0.5, labels=cl)
+        assert np.array_equal(ka[b, :int(kc[b])].cpu().numpy(), src[keep])
+
+
+def test_nms_simple_and_iou_helpers(cuda_lib):
+    from oracle import ref_port as orc, c_oracle
+    from yolo_scratch_b200.train_yolo11_cuda import nms_simple, calculate_iou_batch_simple
+    from yolo_scratch_b200.utils import calculate_iou_batch
+    g = torch.Generator().manual_seed(320)
+    for n in (1, 2, 33, 700, 5000):
+        xy = torch.rand(n, 2, generator=g) * 300
+        wh = torch.rand(n, 2, generator=g) * 80 + 2
+        boxes = torch.cat((xy, xy + wh), 1)
+        scores = torch.rand(n, generator=g)
+        scores[::5] = scores[0]        # ties -> lower index first
+        keep = nms_simple(boxes.cuda(), scores.cuda(), 0.45)
+        assert keep == c_oracle.nms(boxes, scores, 0.45)
+        if n <= 700:
+            assert keep == orc.nms_greedy(boxes, scores, 0.45)
+    assert nms_simple(torch.zeros(0, 4).cuda(), torch.zeros(0).cuda(), 0.5) == []
+    m = calculate_iou_batch(boxes[:50].cuda(), boxes[:70].cuda()).cpu()
+    assert torch.equal(m, orc.iou_matrix(boxes[:50], boxes[:70]))
+    v = calculate_iou_batch_simple(boxes[:1].cuda(), boxes[:70].cuda()).cpu()
+    assert v.shape == (70,) and torch.equal(v, orc.iou_matrix(boxes[:1], boxes[:70]).squeeze(0))
+
+
+def test_nms_nothing_passes_and_everything_suppressed(cuda_lib):
+    from yolo_scratch_b200.train_yolo11_cuda import decode_predictions_for_metrics
+    pred = synth.make_nms_predictions(2, 500, 4, 640, seed=330)
+    res = decode_predictions_for_metrics(pred.cuda(), 640, 2.0, 0.5, torch.device("cuda"))
+    assert all(r["boxes"].shape == (0, 4) and r["labels"].dtype == torch.int64 for r in res)
+    same = pred.clone()
+    same[:, :, :4] = torch.tensor([100.0, 100.0, 50.0, 50.0])
+    res = decode_predictions_for_metrics(same.cuda(), 640, 0.0, 0.5, torch.device("cuda"))
+    assert all(r["boxes"].shape == (1, 4) for r in res)
+
+
+def test_nms_full_batch_256_properties(cuda_lib):
+    """BASELINE.json configs[3] at full size (B=256): keep lists are score-sorted, pairwise IoU of kept boxes <= thr
+    (checked on a sample), image 0 and image 255 match the C oracle."""
+    from oracle import c_oracle
+    from yolo_scratch_b200.train_yolo11_cuda import nms_batched
+    from yolo_scratch_b200.utils import calculate_iou_batch
+    B = 256
+    base = synth.make_nms_predictions(8, 8400, 80, 640, seed=340)
+    pred = base.repeat(32, 1, 1)
+    pred = pred[torch.arange(B).roll(3)]
+    dev = pred.cuda()
+    ka, kb, ks, kl, kc = nms_batched(dev, 0.001, 0.7, 640)
+    torch.cuda.synchronize()
+    for b in (0, 255):
+        xyxy, sc, cl, src = c_oracle.filter_candidates(pred[b], 0.001)
+        keep = c_oracle.nms(xyxy, sc, 0.7)
+        assert np.array_equal(ka[b, :int(kc[b])].cpu().numpy(), src[keep])
+    for b in (17, 130):
+        k = int(kc[b])
+        assert (ks[b, 1:k] <= ks[b, :k - 1]).all()
+        a = ka[b, :min(k, 1500)].long()
+        x, y, w, h = dev[b, a, 0], dev[b, a, 1], dev[b, a, 2], dev[b, a, 3]
+        bx = torch.stack((x - w / 2, y - h / 2, x + w / 2, y + h / 2), 1)
+        iou = calculate_iou_batch(bx, bx)
+        iou.fill_diagonal_(0)
+        assert (iou <= 0.7).all()

@@ -1,0 +1,248 @@
+// ys_decode.cu -- inference decode (DFL + dist2bbox + sigmoid) and the IoU utility entry points.
+// Replaces models/yolo11_modules.py:180-192, :248-266, :303-312, utils/metrics.py:49-81,
+// train_yolo11_cuda.py:402-437 and the forward of losses/yolo_v8_loss.py:12-61; see include/ys_b200.h.
+#include "ys_assign.cuh"
+
+namespace ys {
+
+constexpr int kDecThreads = 128;
+
+// One block = 128 consecutive anchors of one level of one image; thread = 4 anchors; warp w = box side w and a
+// quarter of the classes (same decomposition as the loss kernel).
+// LAYOUT 0: out (B, 4+nc, A) -- per-channel float4 stores.
+// LAYOUT 1: out (B, A, 4+nc) -- staged through shared memory, then one contiguous coalesced copy.
+template <int LAYOUT>
+__global__ void __launch_bounds__(kDecThreads) k_decode_infer(LevelSet L, int nc, float *__restrict__ out) {
+    extern __shared__ float s_out[];           // LAYOUT 1: [kChunk][R] staging
+    __shared__ float s_d[4][kChunk];
+    const int b = blockIdx.y, chunk = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int l = 0;
+#pragma unroll
+    for (int k = 1; k < YS_MAX_LEVELS; ++k)
+        if (k < L.n && chunk >= L.chunk_off[k]) l = k;
+    const int hw = L.hw[l], w = L.w[l];
+    const float st = L.stride[l];
+    const int c0 = (chunk - L.chunk_off[l]) * kChunk;
+    const int i0 = c0 + lane * 4;
+    const bool live = i0 < hw;
+    const float *xin = L.x[l] + (size_t)b * L.C * hw + i0;
+    const int a0 = L.a_off[l] + i0;
+    const int R = 4 + nc;
+    const int A = L.A;
+
+    float dm[4] = {0.f, 0.f, 0.f, 0.f};
+    if (live) {
+        float4 z[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) z[j] = __ldg(reinterpret_cast<const float4 *>(xin + (size_t)(warp * 16 + j) * hw));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float zz[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) zz[j] = (&z[j].x)[k];
+            float m, es;
+            dm[k] = dfl_expect16(zz, m, es);
+        }
+    }
+    *reinterpret_cast<float4 *>(&s_d[warp][lane * 4]) = make_float4(dm[0], dm[1], dm[2], dm[3]);
+    __syncthreads();
+    if (live && warp == 0) {
+        float o[4][4];   // [cx,cy,w,h][k]
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = i0 + k;
+            const int iy = i / w, ix = i - iy * w;
+            const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
+            const float x1 = gx - s_d[0][lane * 4 + k], y1 = gy - s_d[1][lane * 4 + k];
+            const float x2 = gx + s_d[2][lane * 4 + k], y2 = gy + s_d[3][lane * 4 + k];
+            o[0][k] = (x1 + x2) / 2 * st;      // dist2bbox(xywh=True) * strides  (models/yolo11_modules.py:263, :309-311)
+            o[1][k] = (y1 + y2) / 2 * st;
+            o[2][k] = (x2 - x1) * st;
+            o[3][k] = (y2 - y1) * st;
+        }
+        if (LAYOUT == 0) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                *reinterpret_cast<float4 *>(out + ((size_t)b * R + c) * A + a0) = make_float4(o[c][0], o[c][1], o[c][2], o[c][3]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) s_out[(size_t)(lane * 4 + k) * R + c] = o[c][k];
+        }
+    }
+    if (live) {
+        const int per = (nc + 3) >> 2;
+        const int c_lo = warp * per, c_hi = min(nc, c_lo + per);
+        const float *xc = xin + (size_t)64 * hw;
+#pragma unroll 4
+        for (int c = c_lo; c < c_hi; ++c) {
+            const float4 xv = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)c * hw));
+            const float4 s = make_float4(sigmoidf(xv.x), sigmoidf(xv.y), sigmoidf(xv.z), sigmoidf(xv.w));
+            if (LAYOUT == 0) {
+                *reinterpret_cast<float4 *>(out + ((size_t)b * R + 4 + c) * A + a0) = s;
+            } else {
+                s_out[(size_t)(lane * 4 + 0) * R + 4 + c] = s.x;
+                s_out[(size_t)(lane * 4 + 1) * R + 4 + c] = s.y;
+                s_out[(size_t)(lane * 4 + 2) * R + 4 + c] = s.z;
+                s_out[(size_t)(lane * 4 + 3) * R + 4 + c] = s.w;
+            }
+        }
+    }
+    if (LAYOUT == 1) {
+        __syncthreads();
+        const int rows = min(kChunk, hw - c0);
+        float *dst = out + ((size_t)b * A + L.a_off[l] + c0) * R;
+        const int total = rows * R;
+        for (int i = tid; i < total; i += kDecThreads) dst[i] = s_out[i];
+    }
+}
+
+__global__ void k_pairwise_iou(const float4 *__restrict__ b1, int N, const float4 *__restrict__ b2, int M, int kind,
+                               float *__restrict__ out) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (j >= M || i >= N) return;
+    const float4 p = b1[i], q = b2[j];
+    float v;
+    if (kind == 0) v = iou_nms(p, area_plain(p), q, area_plain(q));
+    else {
+        // bbox_iou(xywh=False) without the assigner's clamp (losses/yolo_v8_loss.py:31-44)
+        const float inter = inter_area(p.x, p.y, p.z, p.w, q.x, q.y, q.z, q.w);
+        const float uni = YS_ADD(YS_SUB(YS_ADD(area_eps_h(p.x, p.y, p.z, p.w), area_eps_h(q.x, q.y, q.z, q.w)), inter), kEpsIou);
+        v = YS_DIV(inter, uni);
+    }
+    out[(size_t)i * M + j] = v;
+}
+
+// Elementwise bbox_iou, all modes (losses/yolo_v8_loss.py:12-61), op order as the reference.
+__global__ void k_bbox_iou(const float4 *__restrict__ box1, const float4 *__restrict__ box2, int n, int xywh, int mode,
+                           float eps, float *__restrict__ out, const float *__restrict__ gout, float4 *__restrict__ grad1) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = box1[i], b = box2[i];
+    float ax1, ay1, ax2, ay2, bx1, by1, bx2, by2, w1, h1, w2, h2;
+    if (xywh) {
+        w1 = a.z; h1 = a.w; w2 = b.z; h2 = b.w;
+        const float hw1 = YS_DIV(w1, 2.f), hh1 = YS_DIV(h1, 2.f), hw2 = YS_DIV(w2, 2.f), hh2 = YS_DIV(h2, 2.f);
+        ax1 = YS_SUB(a.x, hw1); ax2 = YS_ADD(a.x, hw1); ay1 = YS_SUB(a.y, hh1); ay2 = YS_ADD(a.y, hh1);
+        bx1 = YS_SUB(b.x, hw2); bx2 = YS_ADD(b.x, hw2); by1 = YS_SUB(b.y, hh2); by2 = YS_ADD(b.y, hh2);
+    } else {
+        ax1 = a.x; ay1 = a.y; ax2 = a.z; ay2 = a.w; bx1 = b.x; by1 = b.y; bx2 = b.z; by2 = b.w;
+        w1 = YS_SUB(ax2, ax1); h1 = YS_ADD(YS_SUB(ay2, ay1), eps);
+        w2 = YS_SUB(bx2, bx1); h2 = YS_ADD(YS_SUB(by2, by1), eps);
+    }
+    const float inter = inter_area(ax1, ay1, ax2, ay2, bx1, by1, bx2, by2);
+    const float uni = YS_ADD(YS_SUB(YS_ADD(YS_MUL(w1, h1), YS_MUL(w2, h2)), inter), eps);
+    const float iou = YS_DIV(inter, uni);
+    float r = iou;
+    if (mode != 0) {
+        const float cw = YS_SUB(fmaxf2(ax2, bx2), fminf2(ax1, bx1));
+        const float ch = YS_SUB(fmaxf2(ay2, by2), fminf2(ay1, by1));
+        if (mode == 2 || mode == 3) {
+            const float c2 = YS_ADD(YS_ADD(YS_MUL(cw, cw), YS_MUL(ch, ch)), eps);
+            const float sx = YS_SUB(YS_SUB(YS_ADD(bx1, bx2), ax1), ax2), sy = YS_SUB(YS_SUB(YS_ADD(by1, by2), ay1), ay2);
+            const float rho2 = YS_DIV(YS_ADD(YS_MUL(sx, sx), YS_MUL(sy, sy)), 4.f);
+            if (mode == 3) {
+                const float dat = YS_SUB(atanf(YS_DIV(w2, h2)), atanf(YS_DIV(w1, h1)));
+                const float v = YS_MUL(0.40528473456935108578f, YS_MUL(dat, dat));
+                const float alpha = YS_DIV(v, YS_ADD(YS_SUB(v, iou), YS_ADD(1.f, eps)));
+                r = YS_SUB(iou, YS_ADD(YS_DIV(rho2, c2), YS_MUL(v, alpha)));
+            } else {
+                r = YS_SUB(iou, YS_DIV(rho2, c2));
+            }
+        } else {
+            const float c_area = YS_ADD(YS_MUL(cw, ch), eps);
+            r = YS_SUB(iou, YS_DIV(YS_SUB(c_area, uni), c_area));
+        }
+    }
+    out[i] = r;
+    if (grad1) {
+        // supported: xyxy, mode 3 (CIoU), eps = 1e-7  -- the BboxLoss use (losses/yolo_v8_loss.py:299)
+        float g[4];
+        (void)ciou_with_grad(make_float4(ax1, ay1, ax2, ay2), make_float4(bx1, by1, bx2, by2), g);
+        const float go = gout ? gout[i] : 1.f;
+        grad1[i] = make_float4(g[0] * go, g[1] * go, g[2] * go, g[3] * go);
+    }
+}
+
+}  // namespace ys
+
+using namespace ys;
+
+// build_levels lives in ys_loss.cu; re-declare a light version here for the decode entry point
+static int build_levels_dec(LevelSet &L, int n_levels, const float *const *xs, const int *hs, const int *ws,
+                            const float *strides, int nc, int reg_max) {
+    YS_REQUIRE(n_levels >= 1 && n_levels <= YS_MAX_LEVELS, YS_ERR_BAD_ARG, "n_levels must be in [1,%d]", YS_MAX_LEVELS);
+    YS_REQUIRE(reg_max == 16, YS_ERR_UNSUPPORTED, "reg_max must be 16");
+    YS_REQUIRE(nc >= 1, YS_ERR_BAD_ARG, "nc must be >= 1");
+    L.n = n_levels;
+    L.C = 4 * reg_max + nc;
+    int a = 0, ch = 0;
+    for (int i = 0; i < n_levels; ++i) {
+        YS_REQUIRE(xs[i] != nullptr && hs[i] > 0 && ws[i] > 0, YS_ERR_BAD_ARG, "level %d: null pointer or empty shape", i);
+        YS_REQUIRE(((uintptr_t)xs[i] & 15) == 0, YS_ERR_BAD_ARG, "level %d: pointer must be 16-byte aligned", i);
+        YS_REQUIRE((hs[i] * ws[i]) % 4 == 0, YS_ERR_UNSUPPORTED, "level %d: h*w must be a multiple of 4", i);
+        L.x[i] = xs[i]; L.g[i] = nullptr; L.w[i] = ws[i]; L.hw[i] = hs[i] * ws[i]; L.stride[i] = strides[i];
+        L.a_off[i] = a; L.chunk_off[i] = ch;
+        a += L.hw[i];
+        ch += (L.hw[i] + kChunk - 1) / kChunk;
+    }
+    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.chunk_off[i] = ch; }
+    for (int i = n_levels; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; }
+    L.A = a;
+    L.n_chunks = ch;
+    return YS_OK;
+}
+
+extern "C" int ys_decode_infer(int n_levels, const float *const *level_x_host, const int *level_h_host,
+                               const int *level_w_host, const float *level_stride_host, int B, int nc, int reg_max,
+                               float *out, int layout, void *stream_v) {
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    YS_REQUIRE(out != nullptr && ((uintptr_t)out & 15) == 0, YS_ERR_BAD_ARG, "out must be non-null and 16-byte aligned");
+    YS_REQUIRE(B >= 1 && B <= 65535, YS_ERR_BAD_ARG, "B must be in [1,65535]");
+    YS_REQUIRE(layout == 0 || layout == 1, YS_ERR_BAD_ARG, "layout must be 0 or 1");
+    LevelSet L;
+    int rc = build_levels_dec(L, n_levels, level_x_host, level_h_host, level_w_host, level_stride_host, nc, reg_max);
+    if (rc) return rc;
+    dim3 grid(L.n_chunks, B);
+    if (layout == 0) {
+        k_decode_infer<0><<<grid, kDecThreads, 0, stream>>>(L, nc, out);
+    } else {
+        const size_t smem = (size_t)kChunk * (4 + nc) * sizeof(float);
+        YS_REQUIRE(smem <= 200 * 1024, YS_ERR_UNSUPPORTED, "nc too large for the staged layout (%d)", nc);
+        static thread_local bool attr_set = false;
+        if (!attr_set) { cudaFuncSetAttribute(k_decode_infer<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr_set = true; }
+        k_decode_infer<1><<<grid, kDecThreads, smem, stream>>>(L, nc, out);
+    }
+    YS_CHECK_LAUNCH("k_decode_infer");
+    return YS_OK;
+}
+
+extern "C" int ys_pairwise_iou(const float *boxes1, int N, const float *boxes2, int M, int kind, float *out, void *stream_v) {
+    YS_REQUIRE(N >= 0 && M >= 0, YS_ERR_BAD_ARG, "negative size");
+    if (N == 0 || M == 0) return YS_OK;
+    YS_REQUIRE(boxes1 && boxes2 && out, YS_ERR_BAD_ARG, "null pointer");
+    YS_REQUIRE((((uintptr_t)boxes1 | (uintptr_t)boxes2) & 15) == 0, YS_ERR_BAD_ARG, "box pointers must be 16-byte aligned");
+    YS_REQUIRE(kind == 0 || kind == 1, YS_ERR_BAD_ARG, "kind must be 0 or 1");
+    YS_REQUIRE(N <= 65535, YS_ERR_UNSUPPORTED, "N must be <= 65535");
+    dim3 grid((M + 255) / 256, N);
+    k_pairwise_iou<<<grid, 256, 0, (cudaStream_t)stream_v>>>((const float4 *)boxes1, N, (const float4 *)boxes2, M, kind, out);
+    YS_CHECK_LAUNCH("k_pairwise_iou");
+    return YS_OK;
+}
+
+extern "C" int ys_bbox_iou(const float *box1, const float *box2, int n, int xywh, int mode, float eps, float *out,
+                           const float *gout, float *grad_box1, void *stream_v) {
+    YS_REQUIRE(n >= 0, YS_ERR_BAD_ARG, "negative size");
+    if (n == 0) return YS_OK;
+    YS_REQUIRE(box1 && box2 && out, YS_ERR_BAD_ARG, "null pointer");
+    YS_REQUIRE((((uintptr_t)box1 | (uintptr_t)box2 | (uintptr_t)grad_box1) & 15) == 0, YS_ERR_BAD_ARG, "box pointers must be 16-byte aligned");
+    YS_REQUIRE(mode >= 0 && mode <= 3, YS_ERR_BAD_ARG, "mode must be 0..3");
+    if (grad_box1) YS_REQUIRE(!xywh && mode == 3 && eps == 1e-7f, YS_ERR_UNSUPPORTED, "gradient is implemented for xyxy CIoU with eps=1e-7 only");
+    k_bbox_iou<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream_v>>>((const float4 *)box1, (const float4 *)box2, n, xywh, mode, eps, out,
+                                                                   gout, (float4 *)grad_box1);
+    YS_CHECK_LAUNCH("k_bbox_iou");
+    return YS_OK;
+}

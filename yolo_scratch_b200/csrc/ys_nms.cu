@@ -1,0 +1,399 @@
+// ys_nms.cu -- batched greedy NMS (bit-exact keep lists) for the validation path.
+// Replaces decode_predictions_for_metrics / nms_simple / calculate_iou_batch_simple
+// (train_yolo11_cuda.py:265-437 of the reference); see include/ys_b200.h.
+//
+//   k_nms_filter    streaming pass over pred: best class (first max), score > conf, xywh -> xyxy,
+//                   sort key (score bits << 32 | ~anchor), warp-aggregated compaction per image
+//   k_nms_sort      one block per image: bitonic sort of the keys in shared memory (descending; ties ->
+//                   lower anchor index first), gathers boxes / classes into sorted order
+//   k_nms_suppress  one block per image: sorted boxes resident in shared memory; 64-row tiles; the
+//                   64x64 diagonal bitmask tile is built with warp ballots and resolved serially, then the
+//                   kept rows of the tile suppress all later columns in parallel (no N x N matrix in HBM)
+#include "ys_common.cuh"
+
+namespace ys {
+
+constexpr int kFilterThreads = 256;
+constexpr int kSortThreads = 1024;
+constexpr int kSupThreads = 512;
+constexpr int kSortMaxN = 16384;       // keys per image the shared-memory sort handles (128 KB)
+constexpr int kSupSmemBoxes = 11264;   // boxes per image kept resident in shared memory (176 KB + extras)
+
+__device__ __forceinline__ unsigned score_bits_ordered(float s) {
+    unsigned u = __float_as_uint(s);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);   // order-preserving for all finite floats; never 0 for s > -NaN
+}
+__device__ __forceinline__ float score_from_ordered(unsigned o) {
+    unsigned u = (o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o;
+    return __uint_as_float(u);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// filter.  layout 1: pred (B, A, R) rows of R = 4+nc floats; layout 0: pred (B, R, A).
+// One warp handles 32 consecutive anchors.
+// ---------------------------------------------------------------------------------------------------
+template <int LAYOUT>
+__global__ void __launch_bounds__(kFilterThreads)
+k_nms_filter(const float *__restrict__ pred, int B, int A, int nc, float conf, unsigned long long *__restrict__ keys,
+             float4 *__restrict__ boxes, int *__restrict__ cls, int *__restrict__ count) {
+    extern __shared__ float s_rows[];   // LAYOUT 1: per warp 32 rows with odd stride
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int warps_per_img = (A + 31) / 32;
+    const long long gw = (long long)blockIdx.x * (kFilterThreads / 32) + warp;
+    if (gw >= (long long)B * warps_per_img) return;
+    const int b = (int)(gw / warps_per_img);
+    const int a0 = (int)(gw % warps_per_img) * 32;
+    const int a = a0 + lane;
+    const int R = 4 + nc;
+    float cx = 0.f, cy = 0.f, bw = 0.f, bh = 0.f, best = 0.f;
+    int bc = 0;
+    if (LAYOUT == 1) {
+        const int RS = R | 1;
+        float *mine = s_rows + (size_t)warp * 32 * RS;
+        const int rows = min(32, A - a0);
+        const float *src = pred + ((size_t)b * A + a0) * R;
+        const int total = rows * R;
+        for (int i = lane; i < total; i += 32) {
+            int r = i / R, c = i - r * R;
+            mine[r * RS + c] = __ldg(src + i);
+        }
+        __syncwarp();
+        if (a < A) {
+            const float *row = mine + lane * RS;
+            cx = row[0]; cy = row[1]; bw = row[2]; bh = row[3];
+            best = row[4];
+            for (int c = 1; c < nc; ++c) {
+                float v = row[4 + c];
+                if (v > best) { best = v; bc = c; }     // first maximum (torch.max(dim) semantics)
+            }
+        }
+    } else {
+        if (a < A) {
+            const float *col = pred + (size_t)b * R * A + a;
+            cx = __ldg(col); cy = __ldg(col + A); bw = __ldg(col + 2 * (size_t)A); bh = __ldg(col + 3 * (size_t)A);
+            best = __ldg(col + 4 * (size_t)A);
+            for (int c = 1; c < nc; ++c) {
+                float v = __ldg(col + (size_t)(4 + c) * A);
+                if (v > best) { best = v; bc = c; }
+            }
+        }
+    }
+    const bool pass = (a < A) && (best > conf);                         // train_yolo11_cuda.py:307
+    const unsigned m = __ballot_sync(0xffffffffu, pass);
+    if (m == 0) return;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(&count[b], __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (pass) {
+        const int pos = base + __popc(m & ((1u << lane) - 1u));
+        // x - w/2 ... (train_yolo11_cuda.py:324-329); /2 is exact
+        const float hw = bw * 0.5f, hh = bh * 0.5f;
+        keys[(size_t)b * A + pos] = ((unsigned long long)score_bits_ordered(best) << 32) | (unsigned long long)(0xFFFFFFFFu - (unsigned)a);
+        boxes[(size_t)b * A + a] = make_float4(YS_SUB(cx, hw), YS_SUB(cy, hh), YS_ADD(cx, hw), YS_ADD(cy, hh));
+        cls[(size_t)b * A + a] = bc;
+    }
+}
+
+// keys for nms_single: every input box is a candidate
+__global__ void k_nms_keys_single(const float *__restrict__ scores, int N, unsigned long long *__restrict__ keys, int *__restrict__ count) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) keys[i] = ((unsigned long long)score_bits_ordered(scores[i]) << 32) | (unsigned long long)(0xFFFFFFFFu - (unsigned)i);
+    if (i == 0) count[0] = N;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// sort: descending bitonic sort of count[b] keys padded with zeros to a power of two.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSortThreads)
+k_nms_sort(const unsigned long long *__restrict__ keys, const int *__restrict__ count, int A,
+           const float4 *__restrict__ boxes, const int *__restrict__ cls, float4 *__restrict__ sbox,
+           float *__restrict__ sscore, int *__restrict__ scls, int *__restrict__ sanchor) {
+    extern __shared__ unsigned long long s_keys[];
+    const int b = blockIdx.x;
+    const int n = count[b];
+    if (n == 0) return;
+    int P = 1;
+    while (P < n) P <<= 1;
+    const unsigned long long *src = keys + (size_t)b * A;
+    for (int i = threadIdx.x; i < P; i += kSortThreads) s_keys[i] = i < n ? src[i] : 0ull;
+    __syncthreads();
+    for (int k = 2; k <= P; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < (P >> 1); t += kSortThreads) {
+                // t-th compare-exchange of this stage
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const int p = i | j;
+                const bool desc = ((i & k) == 0);
+                const unsigned long long x = s_keys[i], y = s_keys[p];
+                if ((x < y) == desc) { s_keys[i] = y; s_keys[p] = x; }
+            }
+            __syncthreads();
+        }
+    }
+    for (int r = threadIdx.x; r < n; r += kSortThreads) {
+        const unsigned long long key = s_keys[r];
+        const int a = (int)(0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull));
+        const size_t o = (size_t)b * A + r;
+        sbox[o] = boxes[(size_t)b * A + a];
+        sscore[o] = score_from_ordered((unsigned)(key >> 32));
+        scls[o] = cls ? cls[(size_t)b * A + a] : 0;
+        sanchor[o] = a;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// suppress
+// ---------------------------------------------------------------------------------------------------
+// IoU(i, j) > thr with the reference's arithmetic (train_yolo11_cuda.py:418-435, :396).
+__device__ __forceinline__ bool suppresses(const float4 &bi, float area_i, const float4 &bj, float thr) {
+    const float iw = YS_SUB(fminf2(bi.z, bj.z), fmaxf2(bi.x, bj.x));
+    const float ih = YS_SUB(fminf2(bi.w, bj.w), fmaxf2(bi.y, bj.y));
+    if (!(iw > 0.f) || !(ih > 0.f)) {
+        // inter == 0 (or NaN): IoU = 0/(union+1e-6).  Only a non-positive denominator could make that
+        // exceed thr; fall through to the exact path in that (degenerate-box) case.
+        if (iw == iw && ih == ih) {
+            const float area_j = area_plain(bj);
+            const float uni0 = YS_ADD(YS_ADD(area_i, area_j), kEpsNms);   // inter = 0: (a1+a2-0)+eps
+            if (uni0 > 0.f) return 0.f > thr;
+        }
+    }
+    const float area_j = area_plain(bj);
+    const float iou = iou_nms(bi, area_i, bj, area_j);
+    return !(iou <= thr);   // the reference keeps `ious <= thr`; NaN is dropped (:396)
+}
+
+template <bool CLASS_AWARE>
+__global__ void __launch_bounds__(kSupThreads)
+k_nms_suppress(const int *__restrict__ count, int A, const float4 *__restrict__ sbox, const float *__restrict__ sscore,
+               const int *__restrict__ scls, const int *__restrict__ sanchor, float thr, float img_size, int smem_boxes,
+               int *__restrict__ keep_anchor, float4 *__restrict__ keep_boxes, float *__restrict__ keep_scores,
+               int *__restrict__ keep_labels, int *__restrict__ keep_count) {
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    const int b = blockIdx.x;
+    const int n = count[b];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (n == 0) {
+        if (tid == 0) keep_count[b] = 0;
+        return;
+    }
+    const int nwords = (n + 31) / 32;
+    // shared layout: boxes[smem_boxes] (float4) | removed[nwords32] | diag[64] (u64) | tile bookkeeping
+    float4 *s_box = reinterpret_cast<float4 *>(s_raw);
+    const bool resident = n <= smem_boxes;
+    const int nb = resident ? n : 0;
+    unsigned *s_removed = reinterpret_cast<unsigned *>(s_raw + (size_t)(resident ? smem_boxes : 0) * sizeof(float4));
+    const int max_words = (A + 31) / 32;
+    unsigned long long *s_diag = reinterpret_cast<unsigned long long *>(s_removed + ((max_words + 3) & ~3));
+    float4 *s_tile = reinterpret_cast<float4 *>(s_diag + 64);   // 64 boxes of the current row tile
+    float *s_tarea = reinterpret_cast<float *>(s_tile + 64);
+    int *s_tcls = reinterpret_cast<int *>(s_tarea + 64);
+    int *s_kept = s_tcls + 64;                                  // [0] = number kept in tile, [1..64] their tile rows
+    const float4 *gbox = sbox + (size_t)b * A;
+    const int *gcls = scls + (size_t)b * A;
+
+    for (int i = tid; i < nb; i += kSupThreads) s_box[i] = gbox[i];
+    for (int i = tid; i < nwords; i += kSupThreads) s_removed[i] = 0u;
+    __syncthreads();
+    const float4 *boxp = resident ? s_box : gbox;
+
+    for (int t0 = 0; t0 < n; t0 += 64) {
+        const int tn = min(64, n - t0);
+        if (tid < 64) {
+            float4 bx = tid < tn ? boxp[t0 + tid] : make_float4(0.f, 0.f, 0.f, 0.f);
+            s_tile[tid] = bx;
+            s_tarea[tid] = area_plain(bx);
+            if (CLASS_AWARE) s_tcls[tid] = tid < tn ? gcls[t0 + tid] : -1;
+        }
+        __syncthreads();
+        // -- diagonal 64x64 bitmask tile by warp ballots: warp w handles rows w, w+16, w+32, w+48
+        for (int r = warp; r < tn; r += kSupThreads / 32) {
+            const float4 bi = s_tile[r];
+            const float ai = s_tarea[r];
+            unsigned long long bits = 0ull;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int c = h * 32 + lane;
+                bool sup = false;
+                if (c > r && c < tn) {
+                    sup = suppresses(bi, ai, s_tile[c], thr);
+                    if (CLASS_AWARE) sup = sup && (s_tcls[c] == s_tcls[r]);
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, sup);
+                bits |= (unsigned long long)m << (32 * h);
+            }
+            if (lane == 0) s_diag[r] = bits;
+        }
+        __syncthreads();
+        // -- serial resolution of the tile (one thread): kept rows and the rows they remove inside the tile
+        if (tid == 0) {
+            const int w0 = t0 >> 5;
+            unsigned long long rem = (unsigned long long)s_removed[w0];
+            if (tn > 32) rem |= (unsigned long long)s_removed[w0 + 1] << 32;
+            int nk = 0;
+            for (int r = 0; r < tn; ++r) {
+                if (!((rem >> r) & 1ull)) {
+                    s_kept[1 + nk++] = r;
+                    rem |= s_diag[r];
+                }
+            }
+            s_kept[0] = nk;
+            s_removed[w0] = (unsigned)(rem & 0xFFFFFFFFull);
+            if (tn > 32) s_removed[w0 + 1] = (unsigned)(rem >> 32);
+        }
+        __syncthreads();
+        // -- kept rows of this tile suppress every later, still-alive column
+        const int nk = s_kept[0];
+        if (nk > 0) {
+            for (int c = t0 + 64 + tid; c < n; c += kSupThreads) {
+                if ((s_removed[c >> 5] >> (c & 31)) & 1u) continue;
+                const float4 bj = boxp[c];
+                const int cj = CLASS_AWARE ? gcls[c] : 0;
+                bool dead = false;
+                for (int q = 0; q < nk && !dead; ++q) {
+                    const int r = s_kept[1 + q];
+                    if (CLASS_AWARE && s_tcls[r] != cj) continue;
+                    dead = suppresses(s_tile[r], s_tarea[r], bj, thr);
+                }
+                if (dead) atomicOr(&s_removed[c >> 5], 1u << (c & 31));
+            }
+        }
+        __syncthreads();
+    }
+
+    // -- compact the survivors in sorted order (one warp, ballot prefix)
+    if (warp == 0) {
+        int base = 0;
+        for (int c0 = 0; c0 < n; c0 += 32) {
+            const int c = c0 + lane;
+            const bool alive = c < n && !((s_removed[c >> 5] >> (c & 31)) & 1u);
+            const unsigned m = __ballot_sync(0xffffffffu, alive);
+            if (alive) {
+                const size_t o = (size_t)b * A + base + __popc(m & ((1u << lane) - 1u));
+                const size_t s = (size_t)b * A + c;
+                if (keep_anchor) keep_anchor[o] = sanchor[s];
+                if (keep_boxes) {
+                    const float4 bx = sbox[s];
+                    // boxes / img_size, clamp to [0,1]  (train_yolo11_cuda.py:347-350)
+                    float4 q = make_float4(YS_DIV(bx.x, img_size), YS_DIV(bx.y, img_size), YS_DIV(bx.z, img_size), YS_DIV(bx.w, img_size));
+                    q.x = fminf2(fmaxf2(q.x, 0.f), 1.f); q.y = fminf2(fmaxf2(q.y, 0.f), 1.f);
+                    q.z = fminf2(fmaxf2(q.z, 0.f), 1.f); q.w = fminf2(fmaxf2(q.w, 0.f), 1.f);
+                    keep_boxes[o] = q;
+                }
+                if (keep_scores) keep_scores[o] = sscore[s];
+                if (keep_labels) keep_labels[o] = scls[s];
+            }
+            base += __popc(m);
+        }
+        if (lane == 0) keep_count[b] = base;
+    }
+}
+
+struct NmsWorkspace {
+    unsigned long long *keys;
+    float4 *boxes, *sbox;
+    int *cls, *scls, *sanchor, *count;
+    float *sscore;
+    size_t bytes;
+};
+static void carve_nms(NmsWorkspace &W, void *base, size_t cap, int B, int A) {
+    Carver c(base, cap);
+    const size_t n = (size_t)B * A;
+    W.count = c.take<int>((size_t)B + 1);
+    W.keys = c.take<unsigned long long>(n);
+    W.boxes = c.take<float4>(n);
+    W.sbox = c.take<float4>(n);
+    W.cls = c.take<int>(n);
+    W.scls = c.take<int>(n);
+    W.sanchor = c.take<int>(n);
+    W.sscore = c.take<float>(n);
+    W.bytes = align_up(c.off, 256);
+}
+
+static size_t suppress_smem_bytes(int A, int smem_boxes) {
+    const int max_words = (A + 31) / 32;
+    return (size_t)smem_boxes * sizeof(float4) + (size_t)((max_words + 3) & ~3) * 4 + 64 * 8 + 64 * 16 + 64 * 4 + 64 * 4 + 65 * 4 + 64;
+}
+
+static int run_sort_suppress(const NmsWorkspace &W, int B, int A, float iou_thr, float img_size, int class_aware,
+                             const float4 *boxes, const int *cls, int32_t *keep_anchor, float *keep_boxes,
+                             float *keep_scores, int32_t *keep_labels, int32_t *keep_count, cudaStream_t stream) {
+    YS_REQUIRE(A <= kSortMaxN, YS_ERR_UNSUPPORTED, "NMS handles at most %d candidates per image (got %d)", kSortMaxN, A);
+    int P = 1;
+    while (P < A) P <<= 1;
+    const size_t sort_smem = (size_t)P * sizeof(unsigned long long);
+    static thread_local bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k_nms_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortMaxN * 8);
+        cudaFuncSetAttribute(k_nms_suppress<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaFuncSetAttribute(k_nms_suppress<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        attr_set = true;
+    }
+    k_nms_sort<<<B, kSortThreads, sort_smem, stream>>>(W.keys, W.count, A, boxes, cls, W.sbox, W.sscore, W.scls, W.sanchor);
+    YS_CHECK_LAUNCH("k_nms_sort");
+    const int smem_boxes = A <= kSupSmemBoxes ? A : 0;
+    const size_t sup_smem = suppress_smem_bytes(A, smem_boxes);
+    if (class_aware)
+        k_nms_suppress<true><<<B, kSupThreads, sup_smem, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr, img_size,
+                                                                   smem_boxes, keep_anchor, (float4 *)keep_boxes, keep_scores, keep_labels, keep_count);
+    else
+        k_nms_suppress<false><<<B, kSupThreads, sup_smem, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr, img_size,
+                                                                    smem_boxes, keep_anchor, (float4 *)keep_boxes, keep_scores, keep_labels, keep_count);
+    YS_CHECK_LAUNCH("k_nms_suppress");
+    return YS_OK;
+}
+
+}  // namespace ys
+
+using namespace ys;
+
+extern "C" size_t ys_nms_workspace_bytes(int B, int A) {
+    NmsWorkspace W;
+    carve_nms(W, nullptr, 0, B > 0 ? B : 1, A > 0 ? A : 1);
+    return W.bytes;
+}
+
+extern "C" int ys_nms_batched(const float *pred, int layout, int B, int A, int nc, float conf_thr, float iou_thr,
+                              float img_size, int class_aware, int32_t *keep_anchor, float *keep_boxes,
+                              float *keep_scores, int32_t *keep_labels, int32_t *keep_count, void *workspace,
+                              size_t workspace_bytes, void *stream_v) {
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    YS_REQUIRE(pred && keep_count && workspace, YS_ERR_BAD_ARG, "null pointer");
+    YS_REQUIRE(B >= 1 && A >= 1 && nc >= 1, YS_ERR_BAD_ARG, "B, A, nc must be >= 1");
+    YS_REQUIRE(layout == 0 || layout == 1, YS_ERR_BAD_ARG, "layout must be 0 (B,4+nc,A) or 1 (B,A,4+nc)");
+    YS_REQUIRE(!keep_boxes || ((uintptr_t)keep_boxes & 15) == 0, YS_ERR_BAD_ARG, "keep_boxes must be 16-byte aligned");
+    NmsWorkspace W;
+    carve_nms(W, workspace, workspace_bytes, B, A);
+    YS_REQUIRE(W.bytes <= workspace_bytes, YS_ERR_WORKSPACE, "workspace too small: need %zu, got %zu", W.bytes, workspace_bytes);
+    YS_REQUIRE(((uintptr_t)workspace & 255) == 0, YS_ERR_BAD_ARG, "workspace must be 256-byte aligned");
+    cudaMemsetAsync(W.count, 0, sizeof(int) * ((size_t)B + 1), stream);
+    const long long warps = (long long)B * ((A + 31) / 32);
+    const unsigned blocks = (unsigned)((warps + kFilterThreads / 32 - 1) / (kFilterThreads / 32));
+    if (layout == 1) {
+        const size_t smem = (size_t)(kFilterThreads / 32) * 32 * ((4 + nc) | 1) * sizeof(float);
+        YS_REQUIRE(smem <= 200 * 1024, YS_ERR_UNSUPPORTED, "nc too large for the staged filter (%d)", nc);
+        static thread_local bool attr_set = false;
+        if (!attr_set) { cudaFuncSetAttribute(k_nms_filter<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr_set = true; }
+        k_nms_filter<1><<<blocks, kFilterThreads, smem, stream>>>(pred, B, A, nc, conf_thr, W.keys, W.boxes, W.cls, W.count);
+    } else {
+        k_nms_filter<0><<<blocks, kFilterThreads, 0, stream>>>(pred, B, A, nc, conf_thr, W.keys, W.boxes, W.cls, W.count);
+    }
+    YS_CHECK_LAUNCH("k_nms_filter");
+    return run_sort_suppress(W, B, A, iou_thr, img_size, class_aware, W.boxes, W.cls, keep_anchor, keep_boxes, keep_scores,
+                             keep_labels, keep_count, stream);
+}
+
+extern "C" int ys_nms_single(const float *boxes, const float *scores, const int32_t *labels, int N, float iou_thr,
+                             int32_t *keep, int32_t *keep_count, void *workspace, size_t workspace_bytes, void *stream_v) {
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    YS_REQUIRE(boxes && scores && keep && keep_count && workspace, YS_ERR_BAD_ARG, "null pointer");
+    YS_REQUIRE(N >= 1, YS_ERR_BAD_ARG, "N must be >= 1");
+    YS_REQUIRE(((uintptr_t)boxes & 15) == 0, YS_ERR_BAD_ARG, "boxes must be 16-byte aligned");
+    NmsWorkspace W;
+    carve_nms(W, workspace, workspace_bytes, 1, N);
+    YS_REQUIRE(W.bytes <= workspace_bytes, YS_ERR_WORKSPACE, "workspace too small: need %zu, got %zu", W.bytes, workspace_bytes);
+    YS_REQUIRE(((uintptr_t)workspace & 255) == 0, YS_ERR_BAD_ARG, "workspace must be 256-byte aligned");
+    k_nms_keys_single<<<(N + 255) / 256, 256, 0, stream>>>(scores, N, W.keys, W.count);
+    YS_CHECK_LAUNCH("k_nms_keys_single");
+    return run_sort_suppress(W, 1, N, iou_thr, 1.0f, labels != nullptr, (const float4 *)boxes, labels, keep, nullptr, nullptr,
+                             nullptr, keep_count, stream);
+}

@@ -1,0 +1,279 @@
+"""Drop-in for the reference's `losses/yolo_v8_loss.py` (same names, same call signatures, same
+return types), backed by the sm_100a kernels in libys_b200.so.
+
+Reference interface mirrored here (paths relative to /root/reference/yolo_scratch_cuda/):
+  v8DetectionLoss            losses/yolo_v8_loss.py:333-538
+  TaskAlignedAssigner        losses/yolo_v8_loss.py:64-270
+  BboxLoss                   losses/yolo_v8_loss.py:273-324
+  bbox_iou / bbox2dist / make_anchors / dist2bbox   :12-61 / :327-330 / :541-552 / :555-564
+
+`v8DetectionLoss.__call__` runs ONE fused C-ABI call (ys_detection_loss) that does target packing,
+decode, assignment, BCE + CIoU + DFL forward and the full backward, reading the head tensors in their
+native NCHW layout.  There is no CPU or eager-PyTorch fallback: CPU tensors raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+import torch.nn as nn
+
+from .. import _lib
+from .._lib import YsError, check, ptr, stream_ptr
+
+
+# ----------------------------------------------------------------------------------------------
+# small tensor helpers of the reference API (layout only; not on the hot path)
+# ----------------------------------------------------------------------------------------------
+def make_anchors(feats, strides, grid_cell_offset=0.5):
+    """Anchor centres in grid units, level-major then row-major, and the stride column
+    (reference losses/yolo_v8_loss.py:541-552)."""
+    pts, sts = [], []
+    dtype, device = feats[0].dtype, feats[0].device
+    for i, stride in enumerate(strides):
+        h, w = feats[i].shape[2:]
+        ys_, xs_ = torch.meshgrid(torch.arange(h, device=device, dtype=dtype) + grid_cell_offset,
+                                  torch.arange(w, device=device, dtype=dtype) + grid_cell_offset, indexing="ij")
+        pts.append(torch.stack((xs_, ys_), -1).view(-1, 2))
+        sts.append(torch.full((h * w, 1), float(stride), dtype=dtype, device=device))
+    return torch.cat(pts), torch.cat(sts)
+
+
+def dist2bbox(distance, anchor_points, xywh=True, dim=-1):
+    """ltrb distances -> xywh or xyxy boxes (reference losses/yolo_v8_loss.py:555-564)."""
+    lt, rb = distance.chunk(2, dim)
+    x1y1, x2y2 = anchor_points - lt, anchor_points + rb
+    if xywh:
+        return torch.cat(((x1y1 + x2y2) / 2, x2y2 - x1y1), dim)
+    return torch.cat((x1y1, x2y2), dim)
+
+
+def bbox2dist(anchor_points, bbox, reg_max):
+    """xyxy boxes -> clamped ltrb targets (reference losses/yolo_v8_loss.py:327-330)."""
+    x1y1, x2y2 = bbox.chunk(2, -1)
+    return torch.cat((anchor_points - x1y1, x2y2 - anchor_points), -1).clamp_(0, reg_max - 0.01)
+
+
+class _BboxIoU(torch.autograd.Function):
+    """Paired-box IoU family through ys_bbox_iou; gradient wrt box1 for the CIoU/xyxy form BboxLoss uses."""
+
+    @staticmethod
+    def forward(ctx, box1, box2, xywh, mode, eps):
+        lib = _lib.lib()
+        n = box1.shape[0]
+        out = torch.empty(n, device=box1.device, dtype=torch.float32)
+        want_grad = box1.requires_grad
+        ctx.can_grad = (not xywh) and mode == 3 and abs(eps - 1e-7) < 1e-12
+        grad = torch.empty_like(box1) if (want_grad and ctx.can_grad) else None
+        check(lib.ys_bbox_iou(ptr(box1), ptr(box2), n, int(bool(xywh)), mode, float(eps), ptr(out), 0, ptr(grad),
+                              stream_ptr(box1.device)), "ys_bbox_iou")
+        ctx.save_for_backward(grad) if grad is not None else None
+        ctx.has_grad = grad is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        if not ctx.has_grad:
+            if not ctx.can_grad:
+                raise YsError("bbox_iou backward is implemented for xywh=False, CIoU=True, eps=1e-7 (the BboxLoss use)")
+            return None, None, None, None, None
+        (grad,) = ctx.saved_tensors
+        return grad * gout.unsqueeze(-1), None, None, None, None
+
+
+def bbox_iou(box1, box2, xywh=True, GIoU=False, DIoU=False, CIoU=False, eps=1e-7):
+    """IoU / GIoU / DIoU / CIoU of broadcastable boxes (..., 4) -> (..., 1)
+    (reference losses/yolo_v8_loss.py:12-61)."""
+    _lib.require_cuda(box1, "box1")
+    _lib.require_cuda(box2, "box2")
+    shape = torch.broadcast_shapes(box1.shape[:-1], box2.shape[:-1])
+    b1 = box1.expand(*shape, 4).reshape(-1, 4).contiguous().float()
+    b2 = box2.expand(*shape, 4).reshape(-1, 4).contiguous().float()
+    mode = 3 if CIoU else 2 if DIoU else 1 if GIoU else 0
+    out = _BboxIoU.apply(b1, b2, bool(xywh), mode, float(eps))
+    return out.view(*shape, 1)
+
+
+# ----------------------------------------------------------------------------------------------
+# TaskAlignedAssigner
+# ----------------------------------------------------------------------------------------------
+class TaskAlignedAssigner(nn.Module):
+    """Same constructor and forward contract as the reference class (losses/yolo_v8_loss.py:64-180).
+    `topk` is accepted and, as in the reference, never used."""
+
+    def __init__(self, topk=13, num_classes=80, alpha=1.0, beta=6.0, eps=1e-9):
+        super().__init__()
+        self.topk = topk
+        self.num_classes = num_classes
+        self.alpha = alpha
+        self.beta = beta
+        self.eps = eps
+        self._ws = _lib.Workspace()
+
+    @torch.no_grad()
+    def forward(self, pd_scores, pd_bboxes, anc_points, gt_labels, gt_bboxes, mask_gt):
+        _lib.require_cuda(pd_scores, "pd_scores")
+        self.bs = pd_scores.shape[0]
+        self.n_max_boxes = gt_bboxes.shape[1]
+        B, A, nc = pd_scores.shape
+        G = self.n_max_boxes
+        if G == 0:   # reference :100-108 (float fg_mask and a float tensor in place of target_gt_idx)
+            z = torch.zeros_like(pd_scores[..., 0])
+            return (torch.full_like(z, self.num_classes).long(), torch.zeros_like(pd_bboxes),
+                    torch.zeros_like(pd_scores), z, z.clone())
+        dev = pd_scores.device
+        f = lambda t: t.detach().to(device=dev, dtype=torch.float32).contiguous()
+        ps, pb, an, gl, gb, mg = f(pd_scores), f(pd_bboxes), f(anc_points), f(gt_labels), f(gt_bboxes), f(mask_gt)
+        lib = _lib.lib()
+        tl = torch.empty(B, A, device=dev)
+        tb = torch.empty(B, A, 4, device=dev)
+        ts = torch.empty(B, A, self.num_classes, device=dev)
+        fg = torch.empty(B, A, device=dev, dtype=torch.uint8)
+        tgi = torch.empty(B, A, device=dev, dtype=torch.int64)
+        ws = self._ws.get(lib.ys_assign_workspace_bytes(B, A, G), dev)
+        check(lib.ys_assign(B, A, G, self.num_classes, ptr(ps), ptr(pb), ptr(an), ptr(gl), ptr(gb), ptr(mg),
+                            float(self.alpha), float(self.beta), float(self.eps), ptr(tl), ptr(tb), ptr(ts), ptr(fg),
+                            ptr(tgi), 0, ptr(ws), ws.numel(), stream_ptr(dev)), "ys_assign")
+        return tl, tb, ts, fg.bool(), tgi
+
+
+# ----------------------------------------------------------------------------------------------
+# BboxLoss (stand-alone use; the fused loss below does not go through it)
+# ----------------------------------------------------------------------------------------------
+class BboxLoss(nn.Module):
+    """CIoU + DFL on already-gathered tensors (reference losses/yolo_v8_loss.py:273-324).  The CIoU value
+    and its gradient come from ys_bbox_iou; the DFL term uses the two-sided cross-entropy of :312-324."""
+
+    def __init__(self, reg_max=16):
+        super().__init__()
+        self.reg_max = reg_max
+
+    def forward(self, pred_dist, pred_bboxes, anchor_points, target_bboxes, target_scores, target_scores_sum, fg_mask):
+        _lib.require_cuda(pred_dist, "pred_dist")
+        weight = target_scores.sum(-1)[fg_mask].unsqueeze(-1)
+        iou = bbox_iou(pred_bboxes[fg_mask], target_bboxes[fg_mask], xywh=False, CIoU=True)
+        loss_iou = ((1.0 - iou) * weight).sum() / target_scores_sum
+        if self.reg_max > 1:
+            target_ltrb = bbox2dist(anchor_points, target_bboxes, self.reg_max - 1)
+            loss_dfl = self._df_loss(pred_dist[fg_mask].view(-1, self.reg_max), target_ltrb[fg_mask]) * weight
+            loss_dfl = loss_dfl.sum() / target_scores_sum
+        else:
+            loss_dfl = torch.tensor(0.0).to(pred_dist.device)
+        return loss_iou, loss_dfl
+
+    @staticmethod
+    def _df_loss(pred_dist, target):
+        target = target.clamp_(0, pred_dist.shape[-1] - 1 - 0.01)
+        lo = target.long()
+        w_lo = (lo + 1) - target
+        logp = pred_dist.log_softmax(-1).view(*lo.shape, -1)
+        ce_lo = -logp.gather(-1, lo.unsqueeze(-1)).squeeze(-1)
+        ce_hi = -logp.gather(-1, (lo + 1).unsqueeze(-1)).squeeze(-1)
+        return (ce_lo * w_lo + ce_hi * (1 - w_lo)).mean(-1, keepdim=True)
+
+
+# ----------------------------------------------------------------------------------------------
+# fused detection loss
+# ----------------------------------------------------------------------------------------------
+class _FusedDetectionLoss(torch.autograd.Function):
+    """forward = ys_detection_loss (forward AND backward kernels); backward = grad * upstream scalar."""
+
+    @staticmethod
+    def forward(ctx, owner, batch_idx, cls, bboxes, export, *feats):
+        lib = _lib.lib()
+        dev = feats[0].device
+        n = len(feats)
+        B = feats[0].shape[0]
+        want_grad = any(f.requires_grad for f in feats)
+        xs = [f.detach() for f in feats]
+        grads = [torch.empty_like(x) for x in xs] if want_grad else None
+        hs = (C.c_int * n)(*[x.shape[2] for x in xs])
+        ws_ = (C.c_int * n)(*[x.shape[3] for x in xs])
+        st = (C.c_float * n)(*[float(s) for s in owner.stride[:n]])
+        xp = (C.c_void_p * n)(*[x.data_ptr() for x in xs])
+        gp = (C.c_void_p * n)(*[g.data_ptr() for g in grads]) if want_grad else None
+        A = sum(x.shape[2] * x.shape[3] for x in xs)
+        n_gt = int(batch_idx.shape[0])
+        out = torch.empty(4, device=dev, dtype=torch.float32)
+        ws = owner._ws.get(lib.ys_detection_loss_workspace_bytes(B, A, n_gt), dev)
+        pb = tgi = nrm = None
+        if export:
+            pb = torch.empty(B, A, 4, device=dev)
+            tgi = torch.empty(B, A, device=dev, dtype=torch.int32)
+            nrm = torch.empty(B, A, device=dev)
+        # imgsz = feats[0].shape[2:] * stride[0]; x is scaled by imgsz[0], y by imgsz[1] (reference :400, :515)
+        sx = float(xs[0].shape[2]) * float(owner.stride[0])
+        sy = float(xs[0].shape[3]) * float(owner.stride[0])
+        check(lib.ys_detection_loss(n, xp, gp, hs, ws_, st, B, owner.nc, owner.reg_max, ptr(batch_idx), ptr(cls),
+                                    ptr(bboxes), n_gt, sx, sy, owner.hyp_box, owner.hyp_cls, owner.hyp_dfl,
+                                    float(owner.assigner.alpha), float(owner.assigner.beta), ptr(out), ptr(pb),
+                                    ptr(tgi), ptr(nrm), 0, ptr(ws), ws.numel(), stream_ptr(dev)), "ys_detection_loss")
+        if export:
+            owner.last_export = {"pred_bboxes_px": pb, "target_gt_idx": tgi, "norm": nrm}
+        ctx.grads = grads
+        total, items = out[0], out[1:4]
+        ctx.mark_non_differentiable(items)
+        return total, items
+
+    @staticmethod
+    def backward(ctx, g_total, g_items):
+        grads = ctx.grads
+        if grads is None:
+            return (None,) * 5
+        lib = _lib.lib()
+        g = g_total.detach().to(torch.float32).contiguous()
+        for t in grads:   # in place, skipped on the device when the upstream scalar is exactly 1
+            check(lib.ys_scale_inplace(ptr(t), t.numel(), ptr(g), stream_ptr(t.device)), "ys_scale_inplace")
+        ctx.grads = None
+        return (None, None, None, None, None) + tuple(grads)
+
+
+class v8DetectionLoss:
+    """Same constructor and call contract as the reference (losses/yolo_v8_loss.py:333-499):
+    `criterion = v8DetectionLoss(model, tal_topk=10)`; `loss, loss_items = criterion(preds, batch)`."""
+
+    def __init__(self, model, tal_topk=10):
+        self.model = model
+        self.tal_topk = tal_topk
+        detect = None
+        if hasattr(model, "model") and hasattr(model.model, "detect"):
+            detect = model.model.detect
+        elif hasattr(model, "detect"):
+            detect = model.detect
+        else:
+            for m in model.modules():
+                if type(m).__name__ == "Detect":
+                    detect = m
+                    break
+        if detect is None:
+            raise YsError("model has no Detect head")
+        self.nc = detect.nc
+        self.reg_max = detect.reg_max
+        self.stride = detect.stride
+        self.device = next(model.parameters()).device
+        self.assigner = TaskAlignedAssigner(topk=50, num_classes=self.nc, alpha=0.5, beta=4.0)
+        self.bbox_loss = BboxLoss(self.reg_max)
+        self.epoch = 0
+        self.hyp_box = 7.5
+        self.hyp_cls = 0.5
+        self.hyp_dfl = 1.5
+        self.export_assignment = False      # tests: keep decoded boxes / assignment of the last call
+        self.last_export = None
+        self._ws = _lib.Workspace()
+
+    def __call__(self, preds, batch):
+        feats = preds
+        if isinstance(feats, tuple):
+            feats = feats[1] if len(feats) == 2 else feats
+        feats = list(feats)
+        for i, f in enumerate(feats):
+            _lib.require_cuda(f, f"preds[{i}]")
+            if f.dtype != torch.float32 or not f.is_contiguous():
+                feats[i] = f.float().contiguous()
+        dev = feats[0].device
+        bi = batch["batch_idx"].to(device=dev, dtype=torch.int64, non_blocking=True).contiguous().view(-1)
+        cl = batch["cls"].to(device=dev, dtype=torch.int64, non_blocking=True).contiguous().view(-1)
+        bb = batch["bboxes"].to(device=dev, dtype=torch.float32, non_blocking=True).contiguous().view(-1, 4)
+        total, items = _FusedDetectionLoss.apply(self, bi, cl, bb, self.export_assignment, *feats)
+        return total, items
