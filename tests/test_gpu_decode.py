@@ -16,7 +16,9 @@ def test_detect_inference_golden(cuda_lib):
     y = detect_inference(feats, int(g["nc"]))
     ref = t(g["y"])
     assert y.shape == ref.shape
-    assert torch.allclose(y.cpu(), ref, rtol=2e-6, atol=2e-6)
+    # boxes: 1e-6 of the image size (w,h are differences of two ~15-bin expectations times the stride)
+    assert torch.allclose(y.cpu()[:, :4], ref[:, :4], rtol=2e-6, atol=1e-6 * 128)
+    assert torch.allclose(y.cpu()[:, 4:], ref[:, 4:], rtol=2e-6, atol=1e-7)
     y2 = detect_inference(feats, int(g["nc"]), anchor_major=True)
     assert torch.equal(y2.permute(0, 2, 1).contiguous(), y)
 
@@ -32,7 +34,7 @@ def test_detect_inference_640_then_nms_end_to_end(cuda_lib):
         f[:, 64:] += 3.0      # lift some class scores over the threshold
     y = detect_inference([f.cuda() for f in feats], 80, anchor_major=True)
     ref = orc.detect_inference(feats, 80, 16, synth.LEVEL_STRIDES)
-    assert torch.allclose(y.cpu().permute(0, 2, 1), ref, rtol=2e-6, atol=2e-5)
+    assert torch.allclose(y.cpu().permute(0, 2, 1), ref, rtol=2e-6, atol=1e-6 * 640)
     ka, kb, ks, kl, kc = nms_batched(y, 0.25, 0.45, 640)
     yc = y.cpu()
     for b in range(2):
