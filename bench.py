@@ -9,11 +9,11 @@ image): BASELINE.json configs[1] = YOLO11n assign + DFL/CIoU/BCE lo
 batch 64 per GPU, 640 px (A=8400), 80 classes, synthetic COCO-shaped GT (<=20 per image).
 
 One JSON line on rank 0:
-  value      images/s of the whole job; a step = one ys_detection_loss C-ABI call (5 kernels, forward AND
+  value      images/s of the whole job; a step = one ys_detection_loss C-ABI call (3 kernels, forward AND
              backward, gradients written) on inputs resident in HBM, timed with CUDA events, max over ranks.
   e2e        the same metric through the drop-in Python API (v8DetectionLoss.__call__ + backward) with the
              head tensors and targets coming from pinned HOST memory each step and the loss items read back.
-  roofline   the dominant kernel (k_loss_fwd_bwd) re-launched alone over its own timed region:
+  roofline   the dominant kernel (k_loss) re-launched alone over its own timed region:
              algorithmic bytes (2 * A * (4*reg_max+nc) * 4 per image) / CUDA-event time vs MEASURED_PEAKS.json.
   cpu_baseline  the oracle port of the reference's PyTorch path (oracle/ref_port.py) on the host cores.
   nms        side measurement of configs[3] (batched NMS, B=256, conf 0.001 / IoU 0.7), N=1 only.
@@ -196,7 +196,7 @@ def run_b200(args):
     cl = batch["cls"].contiguous().view(-1)
     bb = batch["bboxes"].contiguous()
     out = torch.zeros(4, device=dev)
-    wbytes = lib.ys_detection_loss_workspace_bytes(B_PER_GPU, A, n_gt)
+    wbytes = lib.ys_detection_loss_workspace_bytes(B_PER_GPU, A, n_gt, NC)
     wsb = torch.zeros(wbytes + 4096, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream(dev)
 
@@ -238,19 +238,18 @@ def run_b200(args):
     # ---- roofline: the dominant kernel alone, re-launched over its own timed region (state from the last full call)
     reps = max(args.steps, 20)
     for _ in range(3):
-        call(8)
+        call(4)
     torch.cuda.synchronize(dev)
     k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     k0.record(stream)
     for _ in range(reps):
-        call(8)
+        call(4)
     k1.record(stream)
     torch.cuda.synchronize(dev)
     loss_ms = k0.elapsed_time(k1) / reps
     # per-stage breakdown (each stage timed alone the same way)
     stage_ms = {}
-    for name, bit in (("k_pack_gt", 1), ("k_assign_scan", 2), ("k_assign_fixup", 4), ("k_loss_fwd_bwd", 8),
-                      ("k_loss_finalize", 16)):
+    for name, bit in (("k_pack_gt", 1), ("k_assign", 2), ("k_loss", 4)):
         call()
         torch.cuda.synchronize(dev)
         a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -267,10 +266,10 @@ def run_b200(args):
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get("k_loss_fwd_bwd_dram_bytes_per_launch")
+            traffic = json.load(open(tp)).get("k_loss_dram_bytes_per_launch")
         except Exception:
             traffic = None
-    roofline = {"bound": "hbm", "kernel": "k_loss_fwd_bwd", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "k_loss", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms": loss_ms, "algorithmic_bytes_per_launch": ALG_BYTES_PER_IMG * B_PER_GPU,
                 "whole_step_achieved_gbs_per_gpu": ALG_BYTES_PER_IMG * B_PER_GPU * args.steps / (ms_total * 1e-3) / 1e9,
@@ -310,7 +309,7 @@ def run_b200(args):
     line = {"metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(world), "clocks": clocks, "e2e": e2e, "gpu_launches": 5 * args.steps,
+            "config": workload_config(world), "clocks": clocks, "e2e": e2e, "gpu_launches": 3 * args.steps,
             "roofline": roofline, "loss_items": loss_vec}
 
     if world == 1 and not args.no_cpu:

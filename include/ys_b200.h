@@ -65,13 +65,11 @@ int ys_device_info(int *sm_count, int *cc_major, int *cc_minor);
  *  stages: 0 or YS_STAGE_ALL runs the whole path; a subset re-runs only those kernels on the state a
  *  previous full call left in the SAME workspace (bench.py times the dominant kernel alone this way).
  */
-#define YS_STAGE_PACK 1   /* k_pack_gt        flat GT list -> per-image CSR, pixel boxes */
-#define YS_STAGE_SCAN 2   /* k_assign_scan    decode + pairwise IoU / in-box + preliminary assignment */
-#define YS_STAGE_FIXUP 4  /* k_assign_fixup   forced assignments + target_scores_sum */
-#define YS_STAGE_LOSS 8   /* k_loss_fwd_bwd   BCE + CIoU + DFL forward and backward */
-#define YS_STAGE_FINAL 16 /* k_loss_finalize  ordered reduction of the partial sums */
-#define YS_STAGE_ALL 31
-size_t ys_detection_loss_workspace_bytes(int B, int A, int n_gt);
+#define YS_STAGE_PACK 1   /* k_pack_gt  flat GT list -> per-image CSR, pixel boxes */
+#define YS_STAGE_ASSIGN 2 /* k_assign   decode + scan + forced-assignment fix-up + target_scores_sum */
+#define YS_STAGE_LOSS 4   /* k_loss     BCE + CIoU + DFL forward and backward + ordered final reduction */
+#define YS_STAGE_ALL 7
+size_t ys_detection_loss_workspace_bytes(int B, int A, int n_gt, int nc);
 int ys_detection_loss(int n_levels, const float *const *level_x_host, float *const *level_grad_host,
                       const int *level_h_host, const int *level_w_host, const float *level_stride_host,
                       int B, int nc, int reg_max,

@@ -19,8 +19,8 @@ def test_exports_every_declared_symbol():
 
 def test_workspace_sizes_grow():
     lib = _lib.lib()
-    a = lib.ys_detection_loss_workspace_bytes(2, 8400, 40)
-    b = lib.ys_detection_loss_workspace_bytes(64, 8400, 1280)
+    a = lib.ys_detection_loss_workspace_bytes(2, 8400, 40, 80)
+    b = lib.ys_detection_loss_workspace_bytes(64, 8400, 1280, 80)
     assert 0 < a < b
     assert lib.ys_assign_workspace_bytes(2, 8400, 20) > 0
     assert lib.ys_nms_workspace_bytes(256, 8400) > 256 * 8400 * 8

@@ -27,7 +27,7 @@ PROTOTYPES = {
     "ys_version": (c_int, []),
     "ys_last_error": (C.c_char_p, []),
     "ys_device_info": (c_int, [C.POINTER(c_int)] * 3),
-    "ys_detection_loss_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "ys_detection_loss_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "ys_detection_loss": (c_int, [c_int, C.POINTER(c_void_p), C.POINTER(c_void_p), C.POINTER(c_int), C.POINTER(c_int),
                                   C.POINTER(c_float), c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int,
                                   c_float, c_float, c_float, c_float, c_float, c_float, c_float, c_void_p,

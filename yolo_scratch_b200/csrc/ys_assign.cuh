@@ -1,28 +1,28 @@
-// ys_assign.cuh -- task-aligned assignment kernels, shared by the fused loss
-// (boxes decoded on the fly from the NCHW head levels, GT as a CSR list) and by the dense
-// TaskAlignedAssigner.forward entry point (boxes / scores / padded GT given).
+// ys_assign.cuh -- task-aligned assignment, shared by the fused loss (boxes decoded on the
+// fly from the NCHW head levels, GT as a CSR list) and by the dense TaskAlignedAssigner.forward entry point
+// (boxes / scores / padded GT given).  Replaces losses/yolo_v8_loss.py:78-270 of the reference.
 //
-// Replaces losses/yolo_v8_loss.py:78-270 of the reference.  Structure:
-//   k_assign_scan   one thread per anchor: decode (fused), loop over the image's GT staged in shared
-//                   memory; per anchor: in-box count, first in-box GT, first-max IoU GT -> preliminary
-//                   assignment; per GT (cross-anchor facts the reference gets from its B x G Python
-//                   loops): any anchor inside, owned-anchor count, and first-max-IoU anchor as an
-//                   order-preserving u64 atomicMax key.
-//   k_assign_fixup  one block per image: the forced assignments of the reference's two loops
-//                   (:117-139, :146-162) replayed with exact sequential semantics from the per-GT facts,
-//                   touching only the handful of forced anchors; then the per-image sum of target scores
-//                   and (last block) target_scores_sum.
+// ONE kernel, k_assign:
+//   scan phase   one thread per anchor; the image's GT staged in shared memory.  Pass 0 is the cheap one:
+//                centre-in-box test per GT (count, first hit, per-GT "someone is inside" flag).  Only anchors
+//                that sit inside more than one GT run pass 1, the IoU arg-max over all GT slots (:226-244);
+//                the IEEE division is executed only for pairs whose boxes intersect.  Emits the preliminary
+//                assignment, its target score (norm), per-GT owner counts and a per-block partial sum of norm.
+//   fix-up phase run by the LAST block of each image to finish (threadfence + per-image arrival counter):
+//                the forced assignments of the reference's two Python loops (:117-139, :146-162) replayed with
+//                their exact sequential semantics, touching only the handful of forced anchors.  The per-GT
+//                "best-IoU anchor" (arg-max over all anchors) is computed here, lazily, only for the GT that
+//                need it.  Then the image's sum of target scores; the last image computes target_scores_sum.
 #pragma once
 #include "ys_common.cuh"
 
 namespace ys {
 
 constexpr int kScanThreads = 256;
-constexpr int kGtTile = 256;        // GT boxes staged per shared-memory tile
-constexpr int kFixThreads = 256;
-constexpr int kFixSmemGt = 2048;    // per-image GT count handled with shared-memory counters in the fix-up
+constexpr int kGtTile = 512;        // GT boxes staged per shared-memory tile
+constexpr int kFixSmemGt = 1024;    // per-image GT count the fix-up handles with shared-memory scratch
 
-// Everything the assignment kernels need to know about where boxes, scores and GT come from.
+// Everything the assignment kernel needs to know about where boxes, scores and GT come from.
 struct AssignIO {
     // GT (CSR for fused: off = gt_off[b]; dense: off = b*G, count = G)
     const int *gt_off;          // fused only
@@ -35,19 +35,22 @@ struct AssignIO {
     const float4 *pd_box;       // (B,A) px xyxy
     const float *pd_scores;     // (B,A,nc) probabilities
     const float2 *anc;          // (A) px
-    // per-GT scratch, indexed like gt_box
-    unsigned long long *best_key;
+    // per-GT scratch, indexed like gt_box (zero on entry; re-zeroed by the fix-up)
     int *owned_cnt;
-    int *gt_flags;              // bit0: some anchor centre lies inside
-    int *forced;                // 2 ints per GT: anchor forced by loop 1 / loop 2, -1 = none
+    int *gt_flags;              // 1: some anchor centre lies inside
+    unsigned long long *best_key;   // fix-up scratch when an image has more than kFixSmemGt GT
+    int *forced;                // same: 2 ints per GT
     // per-anchor outputs (B,A)
     float4 *pbox;               // fused: decoded px boxes (written by the scan)
     int *tgi;                   // -1 = background
+    int *lab;                   // class of the assigned GT, -1 = background (may be nullptr)
     float *norm;
     // reductions
+    float *partial;             // (B, gridDim.x) per-block sums of norm
     double *img_sum;            // (B)
     float *tss;                 // [0] = max(sum norm, 1)
-    unsigned *done_counter;
+    unsigned *img_done;         // (B) arrival counters, self-resetting
+    unsigned *done_counter;     // images finished, self-resetting
     int nc;
     float alpha, beta, eps;
 };
@@ -58,24 +61,6 @@ __device__ __forceinline__ int level_of(const LevelSet &L, int a) {
     for (int k = 1; k < YS_MAX_LEVELS; ++k)
         if (k < L.n && a >= L.a_off[k]) l = k;
     return l;
-}
-
-// Softmax expectation over 16 logits: d = sum_j j*softmax(z)_j  (losses/yolo_v8_loss.py:534-536).
-// Also returns the max and the sum of exponentials for the DFL cross-entropy.
-__device__ __forceinline__ float dfl_expect16(const float (&z)[16], float &zmax, float &esum) {
-    float m = z[0];
-#pragma unroll
-    for (int j = 1; j < 16; ++j) m = fmaxf(m, z[j]);
-    float s = 0.f, d = 0.f;
-#pragma unroll
-    for (int j = 0; j < 16; ++j) {
-        float e = expf(z[j] - m);
-        s += e;
-        d += e * (float)j;
-    }
-    zmax = m;
-    esum = s;
-    return d / s;
 }
 
 template <bool FUSED>
@@ -105,137 +90,46 @@ __device__ __forceinline__ float score_at(const AssignIO &io, const LevelSet &L,
 
 template <bool FUSED>
 __device__ __forceinline__ int label_of(const AssignIO &io, int gidx) {
-    int lab = FUSED ? io.gt_label_i[gidx] : (int)io.gt_label_f[gidx];
-    return lab;
+    return FUSED ? io.gt_label_i[gidx] : (int)io.gt_label_f[gidx];
 }
 
-template <bool FUSED>
-__global__ void __launch_bounds__(kScanThreads) k_assign_scan(LevelSet L, AssignIO io) {
-    __shared__ float4 s_box[kGtTile];
-    __shared__ float s_area[kGtTile];
-    __shared__ unsigned long long s_best[kGtTile];
-    __shared__ int s_any[kGtTile];
-    __shared__ unsigned char s_valid[kGtTile];
-
-    const int b = blockIdx.y;
-    const int a = blockIdx.x * kScanThreads + threadIdx.x;
-    const bool live = a < L.A;
-
-    int g0, n;
-    gt_range<FUSED>(io, b, g0, n);
-
-    // ---- this anchor's predicted box (px) and centre (px)
-    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-    float ax = 0.f, ay = 0.f;
-    if (live) {
-        if (FUSED) {
-            int l = level_of(L, a);
-            int i = a - L.a_off[l];
-            int w = L.w[l], hw = L.hw[l];
-            float st = L.stride[l];
-            int iy = i / w, ix = i - iy * w;
-            float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
-            const float *base = L.x[l] + (size_t)b * L.C * hw + i;
-            float d[4];
-#pragma unroll
-            for (int s = 0; s < 4; ++s) {
-                float z[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j) z[j] = __ldg(base + (size_t)(s * 16 + j) * hw);
-                float m, es;
-                d[s] = dfl_expect16(z, m, es);
-            }
-            // dist2bbox in grid units, then * stride (losses/yolo_v8_loss.py:558-559, :412)
-            p.x = YS_MUL(YS_SUB(gx, d[0]), st);
-            p.y = YS_MUL(YS_SUB(gy, d[1]), st);
-            p.z = YS_MUL(YS_ADD(gx, d[2]), st);
-            p.w = YS_MUL(YS_ADD(gy, d[3]), st);
-            ax = YS_MUL(gx, st);
-            ay = YS_MUL(gy, st);
-            io.pbox[(size_t)b * L.A + a] = p;
-        } else {
-            p = io.pd_box[(size_t)b * L.A + a];
-            float2 c = io.anc[a];
-            ax = c.x;
-            ay = c.y;
-        }
-    }
-    const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
-
-    int cnt = 0, first = -1, best_g = 0;
-    float best_ov = -1.f, first_ov = 0.f;
-
-    for (int t0 = 0; t0 < n; t0 += kGtTile) {
-        const int tn = min(kGtTile, n - t0);
-        __syncthreads();
-        for (int j = threadIdx.x; j < tn; j += kScanThreads) {
-            float4 q = io.gt_box[g0 + t0 + j];
-            s_box[j] = q;
-            s_area[j] = area_eps_h(q.x, q.y, q.z, q.w);
-            s_best[j] = 0ull;
-            s_any[j] = 0;
-            s_valid[j] = FUSED ? 1 : (io.gt_valid[g0 + t0 + j] != 0.f);
-        }
-        __syncthreads();
-        if (live) {
-            for (int j = 0; j < tn; ++j) {
-                const float4 q = s_box[j];
-                const float ov = iou_assign(p, area_p, q, s_area[j]);
-                const bool in = centre_in_box(ax, ay, q) && s_valid[j];
-                if (in) {
-                    if (first < 0) { first = t0 + j; first_ov = ov; }
-                    ++cnt;
-                    s_any[j] = 1;
-                }
-                if (ov > best_ov) { best_ov = ov; best_g = t0 + j; }
-                const unsigned long long key = argmax_key(ov, (unsigned)a);
-                if (ov >= 0.f && key > s_best[j]) atomicMax(&s_best[j], key);
-            }
-        }
-        __syncthreads();
-        for (int j = threadIdx.x; j < tn; j += kScanThreads) {
-            if (s_best[j]) atomicMax(&io.best_key[g0 + t0 + j], s_best[j]);
-            if (s_any[j]) io.gt_flags[g0 + t0 + j] = 1;
-        }
-    }
-
-    if (!live) return;
-    // ---- preliminary per-anchor resolve (no forced entries yet): losses/yolo_v8_loss.py:226-244
-    int g = -1;
-    float ov = 0.f;
-    if (cnt > 1) { g = best_g; ov = best_ov; }
-    else if (cnt == 1) { g = first; ov = first_ov; }
-    float nrm = 0.f;
-    if (g >= 0) {
-        atomicAdd(&io.owned_cnt[g0 + g], 1);
-        float sc = score_at<FUSED>(io, L, b, a, label_of<FUSED>(io, g0 + g));
-        nrm = align_norm(sc, ov, io.alpha, io.beta, io.eps);
-    }
-    io.tgi[(size_t)b * L.A + a] = g;
-    io.norm[(size_t)b * L.A + a] = nrm;
+// Assigner overlap with the division skipped when the boxes do not intersect: inter == +0 then, the union is
+// positive for well-formed boxes (x2 >= x1, y2 >= y1) and 0/union == +0 bit-for-bit.
+__device__ __forceinline__ float iou_assign_lazy(float4 p, float area_p, float4 q, float area_q) {
+    float iw = YS_SUB(fminf2(p.z, q.z), fmaxf2(p.x, q.x));
+    float ih = YS_SUB(fminf2(p.w, q.w), fmaxf2(p.y, q.y));
+    if (!(iw > 0.f) || !(ih > 0.f)) return 0.f;
+    const float inter = YS_MUL(iw, ih);
+    const float uni = YS_ADD(YS_SUB(YS_ADD(area_p, area_q), inter), kEpsIou);
+    const float iou = YS_DIV(inter, uni);
+    return iou < 0.f ? 0.f : iou;
 }
 
-// Recompute one anchor's row of mask_pos / overlaps with the forced entries of loops 1 (and 2),
-// warp-parallel over the image's GT.  Returns the resolved GT (>= 0) and its overlap.
+// This anchor's centre (px) and, for the fused path, its grid position.
 template <bool FUSED>
-__device__ __forceinline__ int resolve_row(const AssignIO &io, const LevelSet &L, int b, int k, int g0, int n,
-                                           const int *forced, bool with_loop2, float &ov_out) {
-    const int lane = threadIdx.x & 31;
-    float4 p;
-    float ax, ay;
+__device__ __forceinline__ void anchor_centre(const AssignIO &io, const LevelSet &L, int a, float &ax, float &ay) {
     if (FUSED) {
-        p = io.pbox[(size_t)b * L.A + k];
-        int l = level_of(L, k);
-        int i = k - L.a_off[l];
+        int l = level_of(L, a);
+        int i = a - L.a_off[l];
         int iy = i / L.w[l], ix = i - iy * L.w[l];
         ax = YS_MUL((float)ix + 0.5f, L.stride[l]);
         ay = YS_MUL((float)iy + 0.5f, L.stride[l]);
     } else {
-        p = io.pd_box[(size_t)b * L.A + k];
-        float2 c = io.anc[k];
+        float2 c = io.anc[a];
         ax = c.x;
         ay = c.y;
     }
+}
+
+// Recompute one anchor's row of mask_pos / overlaps with the forced entries of loops 1 (and 2),
+// warp-parallel over the image's GT.  Returns the resolved GT (>= 0, or -1) and its overlap.
+template <bool FUSED>
+__device__ __forceinline__ int resolve_row(const AssignIO &io, const LevelSet &L, int b, int k, int g0, int n,
+                                           const int *forced, bool with_loop2, float &ov_out) {
+    const int lane = threadIdx.x & 31;
+    const float4 p = FUSED ? __ldcg(io.pbox + (size_t)b * L.A + k) : io.pd_box[(size_t)b * L.A + k];
+    float ax, ay;
+    anchor_centre<FUSED>(io, L, k, ax, ay);
     const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
     int cnt = 0;
     unsigned first = 0xFFFFFFFFu;
@@ -265,111 +159,335 @@ __device__ __forceinline__ int resolve_row(const AssignIO &io, const LevelSet &L
     return g;
 }
 
+// Shared-memory layout: the scan phase and the fix-up phase never overlap in time, so they alias one buffer.
+struct ScanSmem {
+    float4 box[kGtTile];
+    float area[kGtTile];
+    int any[kGtTile];
+    int own[kGtTile];
+    unsigned char valid[kGtTile];
+};
+struct FixSmem {
+    unsigned long long key[kFixSmemGt];
+    int cnt[kFixSmemGt];
+    int forced[2 * kFixSmemGt];
+    int needy[kFixSmemGt];
+};
+union AssignSmem {
+    ScanSmem s;
+    FixSmem f;
+};
+
 template <bool FUSED>
-__global__ void __launch_bounds__(kFixThreads) k_assign_fixup(LevelSet L, AssignIO io, int B) {
-    __shared__ int s_cnt[kFixSmemGt];
-    __shared__ int s_forced[2 * kFixSmemGt];
-    __shared__ int s_todo;
-    __shared__ double s_red[kFixThreads / 32];
-    const int b = blockIdx.x;
+__device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, FixSmem &S, int nblk);
+
+template <bool FUSED>
+__global__ void __launch_bounds__(kScanThreads) k_assign(LevelSet L, AssignIO io, int B) {
+    __shared__ AssignSmem sm;
+    __shared__ float s_red[kScanThreads / 32];
+    __shared__ int s_flag;
+    ScanSmem &S = sm.s;
+
+    const int b = blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int a = blockIdx.x * kScanThreads + tid;
+    const bool live = a < L.A;
+
+    int g0, n;
+    gt_range<FUSED>(io, b, g0, n);
+
+    // ---- this anchor's predicted box (px) and centre (px)
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+    float ax = 0.f, ay = 0.f;
+    if (live) {
+        if (FUSED) {
+            const int l = level_of(L, a);
+            const int i = a - L.a_off[l];
+            const int w = L.w[l], hw = L.hw[l];
+            const float st = L.stride[l];
+            const int iy = i / w, ix = i - iy * w;
+            const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
+            const float *base = L.x[l] + (size_t)b * L.C * hw + i;
+            float d[4];
+#pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                float z[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) z[j] = __ldg(base + (size_t)(s * 16 + j) * hw);
+                float m2, inv_s;
+                d[s] = dfl_stats16(z, m2, inv_s);
+            }
+            // dist2bbox in grid units, then * stride (losses/yolo_v8_loss.py:558-559, :412)
+            p.x = YS_MUL(YS_SUB(gx, d[0]), st);
+            p.y = YS_MUL(YS_SUB(gy, d[1]), st);
+            p.z = YS_MUL(YS_ADD(gx, d[2]), st);
+            p.w = YS_MUL(YS_ADD(gy, d[3]), st);
+            ax = YS_MUL(gx, st);
+            ay = YS_MUL(gy, st);
+            io.pbox[(size_t)b * L.A + a] = p;
+        } else {
+            p = io.pd_box[(size_t)b * L.A + a];
+            const float2 c = io.anc[a];
+            ax = c.x;
+            ay = c.y;
+        }
+    }
+    const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
+
+    int cnt = 0, first = -1, best_g = 0;
+    float best_ov = -1.f;
+    const int ntiles = (n + kGtTile - 1) / kGtTile;
+    const bool one_tile = ntiles <= 1;
+
+    // ---- pass 0: centre-in-box per GT (losses/yolo_v8_loss.py:210-224); pass 1: IoU arg-max for multi-hit anchors
+    for (int pass = 0; pass < 2; ++pass) {
+        for (int t = 0; t < ntiles; ++t) {
+            const int t0 = t * kGtTile;
+            const int tn = min(kGtTile, n - t0);
+            if (pass == 0 || !one_tile) {
+                __syncthreads();
+                for (int j = tid; j < tn; j += kScanThreads) {
+                    const float4 q = io.gt_box[g0 + t0 + j];
+                    S.box[j] = q;
+                    S.area[j] = area_eps_h(q.x, q.y, q.z, q.w);
+                    S.any[j] = 0;
+                    S.own[j] = 0;
+                    S.valid[j] = FUSED ? 1 : (io.gt_valid[g0 + t0 + j] != 0.f);
+                }
+                __syncthreads();
+            }
+            if (pass == 0) {
+                if (live) {
+                    for (int j = 0; j < tn; ++j) {
+                        if (centre_in_box(ax, ay, S.box[j]) && S.valid[j]) {
+                            if (first < 0) first = t0 + j;
+                            ++cnt;
+                            S.any[j] = 1;
+                        }
+                    }
+                }
+                if (!one_tile) {
+                    __syncthreads();
+                    for (int j = tid; j < tn; j += kScanThreads)
+                        if (S.any[j]) io.gt_flags[g0 + t0 + j] = 1;
+                }
+            } else if (cnt > 1) {
+                for (int j = 0; j < tn; ++j) {
+                    const float ov = iou_assign_lazy(p, area_p, S.box[j], S.area[j]);
+                    if (ov > best_ov) { best_ov = ov; best_g = t0 + j; }     // first maximum over ALL slots (:233)
+                }
+            }
+        }
+        if (pass == 0 && !__syncthreads_or(cnt > 1)) break;
+    }
+
+    // ---- preliminary per-anchor resolve (no forced entries yet): losses/yolo_v8_loss.py:226-244
+    int g = -1;
+    float ov = 0.f;
+    if (cnt > 1) { g = best_g; ov = best_ov; }
+    else if (cnt == 1) {
+        g = first;
+        const float4 q = one_tile ? S.box[first] : io.gt_box[g0 + first];
+        ov = iou_assign(p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
+    }
+    float nrm = 0.f;
+    int lb = -1;
+    if (g >= 0) {
+        if (one_tile) atomicAdd(&S.own[g], 1);
+        else atomicAdd(&io.owned_cnt[g0 + g], 1);
+        lb = label_of<FUSED>(io, g0 + g);
+        const float sc = score_at<FUSED>(io, L, b, a, lb);
+        nrm = align_norm(sc, ov, io.alpha, io.beta, io.eps);
+    }
+    if (live) {
+        io.tgi[(size_t)b * L.A + a] = g;
+        io.norm[(size_t)b * L.A + a] = nrm;
+        if (io.lab) io.lab[(size_t)b * L.A + a] = lb;
+    }
+    // ---- block partial of sum(norm), fixed order; per-GT facts of this block
+    float part = warp_sum(nrm);
+    if (lane == 0) s_red[warp] = part;
+    __syncthreads();
+    if (one_tile) {
+        for (int j = tid; j < n; j += kScanThreads) {
+            if (S.own[j]) atomicAdd(&io.owned_cnt[g0 + j], S.own[j]);
+            if (S.any[j]) io.gt_flags[g0 + j] = 1;
+        }
+    }
+    if (tid == 0) {
+        float tsum = 0.f;
+#pragma unroll
+        for (int w = 0; w < kScanThreads / 32; ++w) tsum += s_red[w];
+        io.partial[(size_t)b * gridDim.x + blockIdx.x] = tsum;
+    }
+
+    // ---- last block of this image runs the fix-up
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned prev = atomicAdd(&io.img_done[b], 1u);
+        s_flag = (prev == gridDim.x - 1u);
+    }
+    __syncthreads();
+    if (!s_flag) return;
+    __threadfence();
+    fixup_image<FUSED>(L, io, b, B, sm.f, (int)gridDim.x);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Fix-up of one image (all kScanThreads threads of the last block to finish that image).
+// ---------------------------------------------------------------------------------------------------
+template <bool FUSED>
+__device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, FixSmem &S, int nblk) {
+    __shared__ int s_todo, s_nneedy;
+    __shared__ double s_delta;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int g0, n;
     gt_range<FUSED>(io, b, g0, n);
-    int *tgi = io.tgi + (size_t)b * L.A;
-    float *norm = io.norm + (size_t)b * L.A;
+    volatile int *tgi = io.tgi + (size_t)b * L.A;      // written by other blocks of this launch: no L1
+    int *labp = io.lab ? io.lab + (size_t)b * L.A : nullptr;
+    volatile float *norm = io.norm + (size_t)b * L.A;
     // per-GT scratch: shared memory when the image's GT fit, else the global scratch in place
     const bool in_smem = n <= kFixSmemGt;
-    int *cntp = in_smem ? s_cnt : (io.owned_cnt + g0);
-    int *forced = in_smem ? s_forced : (io.forced + 2 * (size_t)g0);   // [2j] loop-1 anchor, [2j+1] loop-2 anchor
+    int *cntp = in_smem ? S.cnt : (io.owned_cnt + g0);
+    int *forced = in_smem ? S.forced : (io.forced + 2 * (size_t)g0);   // [2j] loop-1 anchor, [2j+1] loop-2 anchor
+    unsigned long long *keyp = in_smem ? S.key : (io.best_key + g0);
+    int *needy = in_smem ? S.needy : nullptr;
 
-    // ---- does this image need any forced assignment?  (common case: no)
-    if (tid == 0) s_todo = 0;
+    if (tid == 0) { s_todo = 0; s_nneedy = 0; s_delta = 0.0; }
     __syncthreads();
-    for (int j = tid; j < n; j += kFixThreads) {
-        bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
-        int c = io.owned_cnt[g0 + j];
-        if (in_smem) s_cnt[j] = c;
-        bool lonely1 = valid && io.gt_flags[g0 + j] == 0;
-        // loop 1 (losses/yolo_v8_loss.py:117-139): valid GT with no anchor inside -> its best-IoU anchor
-        forced[2 * j] = lonely1 ? (int)argmax_key_index(io.best_key[g0 + j]) : -1;
+    // ---- which GT need a forced assignment?  (common case: none)
+    for (int j = tid; j < n; j += kScanThreads) {
+        const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
+        const int c = __ldcg(io.owned_cnt + g0 + j);
+        const int fl = __ldcg(io.gt_flags + g0 + j);
+        if (in_smem) S.cnt[j] = c;
+        const bool lonely1 = valid && fl == 0;           // loop 1 (:117-139): valid GT with no anchor centre inside
+        forced[2 * j] = lonely1 ? -2 : -1;               // -2: pending, resolved below
         forced[2 * j + 1] = -1;
-        if (valid && (lonely1 || c == 0)) s_todo = 1;
+        keyp[j] = 0ull;
+        if (valid && (lonely1 || c == 0)) {               // loop 2 (:146-162) can only fire for GT that own nothing now
+            s_todo = 1;
+            if (in_smem) needy[atomicAdd(&s_nneedy, 1)] = j;
+        }
     }
     __syncthreads();
-    if (s_todo && warp == 0) {
-        // -- first resolve (:142) for the anchors loop 1 touched; everyone else keeps the scan's result
-        for (int j = 0; j < n; ++j) {
-            int k = forced[2 * j];
-            if (k < 0) continue;
-            bool seen = false;   // k already handled through an earlier GT?
-            for (int jj = lane; jj < j; jj += 32) seen |= (forced[2 * jj] == k);
-            if (__any_sync(0xffffffffu, seen)) continue;
-            float ov;
-            int gnew = resolve_row<FUSED>(io, L, b, k, g0, n, forced, false, ov);
-            if (lane == 0) {
-                int gold = tgi[k];
-                if (gold >= 0) cntp[gold] -= 1;
-                if (gnew >= 0) cntp[gnew] += 1;
-                tgi[k] = gnew;
+    if (s_todo) {
+        // -- arg-max over all anchors of IoU(anchor, GT j) (first maximum) for the GT that may need it (:136, :156)
+        const int nn = in_smem ? s_nneedy : n;
+        for (int a = tid; a < L.A; a += kScanThreads) {
+            const float4 p = FUSED ? __ldcg(io.pbox + (size_t)b * L.A + a) : io.pd_box[(size_t)b * L.A + a];
+            const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
+            for (int q = 0; q < nn; ++q) {
+                const int j = in_smem ? needy[q] : q;
+                const float4 gq = io.gt_box[g0 + j];
+                const float ov = iou_assign_lazy(p, area_p, gq, area_eps_h(gq.x, gq.y, gq.z, gq.w));
+                const unsigned long long key = argmax_key(ov, (unsigned)a);
+                if (key > *((volatile unsigned long long *)&keyp[j])) atomicMax(&keyp[j], key);
             }
-            __syncwarp();
         }
-        // -- loop 2 (:146-162): sequential in g; later GT see the edits of earlier ones
-        if (lane == 0) {
+        __syncthreads();
+        for (int j = tid; j < n; j += kScanThreads)
+            if (forced[2 * j] == -2) forced[2 * j] = (int)argmax_key_index(keyp[j]);
+        __syncthreads();
+        if (warp == 0) {
+            // -- first resolve (:142) for the anchors loop 1 touched; everyone else keeps the scan's result
             for (int j = 0; j < n; ++j) {
-                bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
-                if (!valid || cntp[j] != 0) continue;
-                int k = (int)argmax_key_index(io.best_key[g0 + j]);
-                forced[2 * j + 1] = k;
-                int gold = tgi[k];
-                if (gold >= 0) cntp[gold] -= 1;
-                tgi[k] = j;
-                cntp[j] += 1;
-            }
-        }
-        __syncwarp();
-        // -- final resolve (:165) from mask_pos alone, for every anchor that carries a forced entry
-        for (int j = 0; j < 2 * n; ++j) {
-            int k = forced[j];
-            if (k < 0) continue;
-            bool seen = false;
-            for (int jj = lane; jj < j; jj += 32) seen |= (forced[jj] == k);
-            if (__any_sync(0xffffffffu, seen)) continue;
-            float ov;
-            int gfin = resolve_row<FUSED>(io, L, b, k, g0, n, forced, true, ov);
-            if (lane == 0) {
-                tgi[k] = gfin;
-                float nrm = 0.f;
-                if (gfin >= 0) {
-                    float sc = score_at<FUSED>(io, L, b, k, label_of<FUSED>(io, g0 + gfin));
-                    nrm = align_norm(sc, ov, io.alpha, io.beta, io.eps);
+                const int k = forced[2 * j];
+                if (k < 0) continue;
+                bool seen = false;   // k already handled through an earlier GT?
+                for (int jj = lane; jj < j; jj += 32) seen |= (forced[2 * jj] == k);
+                if (__any_sync(0xffffffffu, seen)) continue;
+                float ov;
+                const int gnew = resolve_row<FUSED>(io, L, b, k, g0, n, forced, false, ov);
+                if (lane == 0) {
+                    const int gold = tgi[k];
+                    if (gold >= 0) cntp[gold] -= 1;
+                    if (gnew >= 0) cntp[gnew] += 1;
+                    tgi[k] = gnew;
                 }
-                norm[k] = nrm;
+                __syncwarp();
             }
-            __syncwarp();
+            // -- loop 2 (:146-162): sequential in g; later GT see the edits of earlier ones
+            for (int j = 0; j < n; ++j) {
+                const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
+                if (!valid || cntp[j] != 0) continue;              // warp-uniform (shared / L2 state, read after __syncwarp)
+                unsigned long long key = keyp[j];
+                if (key == 0ull) {
+                    // a GT that lost its only anchor in the first resolve: its arg-max was not precomputed
+                    const float4 gq = io.gt_box[g0 + j];
+                    const float area_q = area_eps_h(gq.x, gq.y, gq.z, gq.w);
+                    for (int a = lane; a < L.A; a += 32) {
+                        const float4 p = FUSED ? __ldcg(io.pbox + (size_t)b * L.A + a) : io.pd_box[(size_t)b * L.A + a];
+                        const float ov = iou_assign_lazy(p, area_eps_h(p.x, p.y, p.z, p.w), gq, area_q);
+                        const unsigned long long kk = argmax_key(ov, (unsigned)a);
+                        key = kk > key ? kk : key;
+                    }
+                    key = warp_max(key);
+                }
+                if (lane == 0) {
+                    const int k = (int)argmax_key_index(key);
+                    keyp[j] = key;
+                    forced[2 * j + 1] = k;
+                    const int gold = tgi[k];
+                    if (gold >= 0) cntp[gold] -= 1;
+                    tgi[k] = j;
+                    cntp[j] += 1;
+                }
+                __syncwarp();
+            }
+            // -- final resolve (:165) from mask_pos alone, for every anchor that carries a forced entry
+            double delta = 0.0;
+            for (int j = 0; j < 2 * n; ++j) {
+                const int k = forced[j];
+                if (k < 0) continue;
+                bool seen = false;
+                for (int jj = lane; jj < j; jj += 32) seen |= (forced[jj] == k);
+                if (__any_sync(0xffffffffu, seen)) continue;
+                float ov;
+                const int gfin = resolve_row<FUSED>(io, L, b, k, g0, n, forced, true, ov);
+                if (lane == 0) {
+                    tgi[k] = gfin;
+                    float nrm = 0.f;
+                    int lb = -1;
+                    if (gfin >= 0) {
+                        lb = label_of<FUSED>(io, g0 + gfin);
+                        const float sc = score_at<FUSED>(io, L, b, k, lb);
+                        nrm = align_norm(sc, ov, io.alpha, io.beta, io.eps);
+                    }
+                    delta += (double)nrm - (double)norm[k];
+                    norm[k] = nrm;
+                    if (labp) labp[k] = lb;
+                }
+                __syncwarp();
+            }
+            if (lane == 0) s_delta = delta;
         }
     }
     __syncthreads();
-
-    // ---- per-image sum of target scores (fixed order), then target_scores_sum in the last block
-    double acc = 0.0;
-    for (int a = tid; a < L.A; a += kFixThreads) acc += (double)norm[a];
-    acc = warp_sum(acc);
-    if (lane == 0) s_red[warp] = acc;
-    __syncthreads();
-    if (tid == 0) {
-        double t = 0.0;
-        for (int w = 0; w < kFixThreads / 32; ++w) t += s_red[w];
-        io.img_sum[b] = t;
-        __threadfence();
-        unsigned prev = atomicAdd(io.done_counter, 1u);
-        if (prev == (unsigned)B - 1u) {
+    // ---- leave the per-GT scratch zeroed for the next call
+    for (int j = tid; j < n; j += kScanThreads) {
+        io.owned_cnt[g0 + j] = 0;
+        io.gt_flags[g0 + j] = 0;
+    }
+    // ---- per-image sum of target scores (fixed order), then target_scores_sum in the last image
+    if (warp == 0) {
+        double acc = 0.0;
+        for (int i = lane; i < nblk; i += 32) acc += (double)__ldcg(io.partial + (size_t)b * nblk + i);
+        acc = warp_sum(acc);
+        if (lane == 0) {
+            io.img_sum[b] = acc + s_delta;
+            io.img_done[b] = 0u;
             __threadfence();
-            double tot = 0.0;
-            for (int i = 0; i < B; ++i) tot += ((volatile double *)io.img_sum)[i];
-            float tss = (float)tot;
-            io.tss[0] = tss > 1.f ? tss : 1.f;     // max(target_scores.sum(), 1)  (:472)
-            *io.done_counter = 0u;
+            const unsigned prev = atomicAdd(io.done_counter, 1u);
+            if (prev == (unsigned)B - 1u) {
+                __threadfence();
+                double tot = 0.0;
+                for (int i = 0; i < B; ++i) tot += __ldcg(io.img_sum + i);
+                const float tss = (float)tot;
+                io.tss[0] = tss > 1.f ? tss : 1.f;     // max(target_scores.sum(), 1)  (:472)
+                *io.done_counter = 0u;
+            }
         }
     }
 }

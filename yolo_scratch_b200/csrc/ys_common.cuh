@@ -40,10 +40,13 @@ struct LevelSet {
     int hw[YS_MAX_LEVELS];
     int a_off[YS_MAX_LEVELS + 1];       // first anchor of each level; a_off[n] = A
     int chunk_off[YS_MAX_LEVELS + 1];   // first chunk of each level
+    int seg_off[YS_MAX_LEVELS + 1];     // first 32-anchor segment of each level (box role of the loss kernel)
+    int n_segs;                         // total 32-anchor segments per image
     float stride[YS_MAX_LEVELS];
 };
 
-constexpr int kChunk = 128;   // anchors per loss-kernel work item (32 lanes x float4)
+constexpr int kChunk = 128;   // anchors per class-role work item of the loss kernel (32 lanes x float4)
+constexpr int kSeg = 32;      // anchors per box-role work item (one lane per anchor, one 128-byte line per channel row)
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 

@@ -41,8 +41,8 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer(LevelSet L, int nc
             float zz[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j) zz[j] = (&z[j].x)[k];
-            float m, es;
-            dm[k] = dfl_expect16(zz, m, es);
+            float m2, inv_s;
+            dm[k] = dfl_stats16(zz, m2, inv_s);
         }
     }
     *reinterpret_cast<float4 *>(&s_d[warp][lane * 4]) = make_float4(dm[0], dm[1], dm[2], dm[3]);

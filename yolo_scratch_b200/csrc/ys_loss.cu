@@ -1,12 +1,12 @@
 // ys_loss.cu -- fused detection loss (assign + BCE + CIoU + DFL, forward and backward) and the dense
 // TaskAlignedAssigner entry point.  Replaces losses/yolo_v8_loss.py of the reference; see include/ys_b200.h.
 //
-// Launch sequence of ys_detection_loss (one stream, no host sync):
-//   k_pack_gt        flat GT list -> per-image CSR (stable), pixel boxes        [replaces preprocess :501-527]
-//   k_assign_scan    decode + pairwise IoU / in-box + preliminary assignment    [reads the 64 box channels]
-//   k_assign_fixup   forced assignments of the two reference loops, tss         [tiny]
-//   k_loss_fwd_bwd   BCE + CIoU + DFL forward and backward, NCHW in, NCHW out   [reads 144 ch, writes 144 ch]
-//   k_loss_finalize  ordered fp64 reduction of the per-block partial sums        [tiny]
+// Launch sequence of ys_detection_loss (one stream, no host sync, three kernels):
+//   k_pack_gt   flat GT list -> per-image CSR (stable), pixel boxes                     [replaces preprocess :501-527]
+//   k_assign    decode + in-box / IoU scan + preliminary assignment; the last block of each image replays the
+//               reference's forced-assignment loops; the last image computes target_scores_sum  [reads 64 box channels]
+//   k_loss      BCE + CIoU + DFL forward and backward, NCHW in, NCHW out; the last block reduces the partial
+//               sums in a fixed order                                                   [reads 144 ch, writes 144 ch]
 #include "ys_assign.cuh"
 
 namespace ys {
@@ -21,13 +21,15 @@ __global__ void __launch_bounds__(kPackThreads)
 k_pack_gt(const long long *__restrict__ batch_idx, const long long *__restrict__ cls, const float4 *__restrict__ bboxes,
           int N, int B, int nc, float sx, float sy, int *__restrict__ gt_off, int *__restrict__ rank,
           int *__restrict__ cursor_g, float4 *__restrict__ gt_box, int *__restrict__ gt_label,
-          unsigned long long *__restrict__ best_key, int *__restrict__ owned_cnt, int *__restrict__ gt_flags) {
+          unsigned long long *__restrict__ best_key, int *__restrict__ owned_cnt, int *__restrict__ gt_flags,
+          unsigned *__restrict__ counters, int n_counters) {
     __shared__ int s_cursor[kPackSmemB];
     __shared__ int s_part[kPackThreads / 32];
     __shared__ int s_unsorted;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     volatile int *cursor = (B <= kPackSmemB) ? (volatile int *)s_cursor : (volatile int *)cursor_g;
     for (int i = tid; i < B; i += kPackThreads) cursor[i] = 0;
+    for (int i = tid; i < n_counters; i += kPackThreads) counters[i] = 0u;    // arrival counters of k_assign / k_loss
     if (tid == 0) s_unsorted = 0;
     __syncthreads();
     // sorted and all ids valid?  (what the reference collate produces)
@@ -139,176 +141,211 @@ k_pack_gt(const long long *__restrict__ batch_idx, const long long *__restrict__
 // =====================================================================================================
 // Loss forward + backward
 // =====================================================================================================
-constexpr int kLossThreads = 128;   // 4 warps: warp w owns box side w (16 channels) and a quarter of the classes
+// One launch, two warp roles, every warp an independent work item (no intra-block exchange until the final
+// partial sums).  Work items are numbered image-major so both roles of an image run close in time:
+//   box role    one warp = one 32-anchor segment of one level of one image, one lane per anchor, 64 box
+//               channels.  Each channel row of a segment is one 128-byte line.  Segments without a foreground
+//               anchor only zero-fill their gradient rows; foreground lanes run softmax statistics -> decode ->
+//               CIoU value + gradient -> DFL cross-entropy, then stream the 64 gradients out.
+//   class role  one warp = 128 anchors (float4 per lane) x 16 class channels.  BCE-with-logits forward and
+//               backward per element: one ex2, one rcp, a degree-7 polynomial for log1p -- no divisions.
+// The last block to finish reduces the per-block partial sums in a fixed order (fp64) and writes the loss.
+constexpr int kLossThreads = 256;
+constexpr int kLossWarps = kLossThreads / 32;
+constexpr int kClsGroup = 16;       // class channels per class-role work item
+constexpr int kClsBatch = 4;        // float4 loads in flight per lane
 
 struct LossParams {
     const int *tgi;          // (B,A) -1 = background
+    const int *lab;          // (B,A) class of the assigned GT, -1 = background
     const float *norm;       // (B,A)
     const int *gt_off;       // (B+1)
     const float4 *gt_box;    // px
-    const int *gt_label;
     const float *tss;        // [0]
-    float *partials;         // (gridDim.x*gridDim.y, 4): box, cls, dfl partial sums (unnormalised)
-    int nc;
+    float4 *partials;        // (gridDim.x): box, cls, dfl partial sums (unnormalised)
+    unsigned *done;          // arrival counter, self-resetting
+    float *loss_out;         // [4]
+    int nc, n_groups;        // class channels, ceil(nc / kClsGroup)
+    int items_per_img;       // n_segs + n_chunks * n_groups
+    int total_items;         // B * items_per_img
     float hyp_box, hyp_cls, hyp_dfl;
     float batch;             // (float)B
 };
 
+// Register-resident 4-entry tables indexed by a loop counter that is deliberately NOT unrolled (keeps one side's
+// 16 logits live at a time instead of letting the compiler hoist all 64 loads).
+template <typename T> __device__ __forceinline__ T sel4(const T (&a)[4], int s) {
+    return s == 0 ? a[0] : (s == 1 ? a[1] : (s == 2 ? a[2] : a[3]));
+}
+template <typename T> __device__ __forceinline__ void put4(T (&a)[4], int s, T v) {
+    a[0] = s == 0 ? v : a[0]; a[1] = s == 1 ? v : a[1]; a[2] = s == 2 ? v : a[2]; a[3] = s == 3 ? v : a[3];
+}
+
 template <bool WRITE_GRAD>
-__global__ void __launch_bounds__(kLossThreads) k_loss_fwd_bwd(LevelSet L, LossParams P) {
-    __shared__ float s_d[4][kChunk];       // ltrb expectation per side per anchor of the chunk
-    __shared__ float s_sum[4][3];
+__device__ __forceinline__ void loss_box_segment(const LevelSet &L, const LossParams &P, int b, int seg, int lane,
+                                                 float inv_tss, float &acc_box, float &acc_dfl) {
+    int l = 0;
+#pragma unroll
+    for (int k = 1; k < YS_MAX_LEVELS; ++k)
+        if (k < L.n && seg >= L.seg_off[k]) l = k;
+    const int hw = L.hw[l], w = L.w[l];
+    const float st = L.stride[l];
+    const int i = (seg - L.seg_off[l]) * kSeg + lane;
+    const bool live = i < hw;
+    const size_t img = (size_t)b * L.C * hw;
+    const float *xin = L.x[l] + img + i;
+    float *gout = WRITE_GRAD ? (L.g[l] + img + i) : nullptr;
+    const int tg = live ? __ldg(P.tgi + (size_t)b * L.A + L.a_off[l] + i) : -1;
+    const bool fg = tg >= 0;
+    if (!__any_sync(0xffffffffu, fg)) {
+        if (WRITE_GRAD && live) {
+#pragma unroll 16
+            for (int c = 0; c < 64; ++c) gout[(size_t)c * hw] = 0.f;
+        }
+        return;
+    }
+    float gd[4] = {0.f, 0.f, 0.f, 0.f};       // d(total)/d(d_s) from the CIoU term
+    float dd[4] = {0.f, 0.f, 0.f, 0.f};       // ltrb expectation
+    float m2[4] = {0.f, 0.f, 0.f, 0.f}, inv_s[4] = {1.f, 1.f, 1.f, 1.f};
+    float wl[4] = {0.f, 0.f, 0.f, 0.f};
+    int tl[4] = {0, 0, 0, 0};
+    float cdfl = 0.f;
+    if (fg) {
+        const float wgt = __ldg(P.norm + (size_t)b * L.A + L.a_off[l] + i);           // target_scores.sum(-1) (:298)
+        const float4 q = __ldg(P.gt_box + __ldg(P.gt_off + b) + tg);
+        const float4 tb = make_float4(q.x / st, q.y / st, q.z / st, q.w / st);        // target_bboxes /= stride (:479)
+        const int iy = i / w, ix = i - iy * w;
+        const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
+        // DFL targets (:304, :327-330, :315)
+        float tt[4] = {gx - tb.x, gy - tb.y, tb.z - gx, tb.w - gy};
+        float ce = 0.f;
+#pragma unroll 1
+        for (int s = 0; s < 4; ++s) {
+            float z[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) z[j] = __ldg(xin + (size_t)(s * 16 + j) * hw);
+            float m2s, invs;
+            const float ds = dfl_stats16(z, m2s, invs);
+            const float t = fminf(fmaxf(sel4(tt, s), 0.f), 14.99f);                   // reg_max - 1 - 0.01
+            const int tli = (int)t;
+            const float wls = (float)(tli + 1) - t;
+            // cross-entropy at bins tl and tl+1: lse - z[bin]; lse = (m2 - log2(inv_s)) * ln2
+            const float lse = (m2s - log2f(invs)) * 0.69314718055994531f;
+            const float zl = __ldg(xin + (size_t)(s * 16 + tli) * hw);
+            const float zr = __ldg(xin + (size_t)(s * 16 + tli + 1) * hw);
+            ce += (lse - zl) * wls + (lse - zr) * (1.0f - wls);
+            put4(dd, s, ds); put4(m2, s, m2s); put4(inv_s, s, invs); put4(wl, s, wls); put4(tl, s, tli);
+        }
+        const float4 pb = make_float4(gx - dd[0], gy - dd[1], gx + dd[2], gy + dd[3]);   // grid units
+        float g4[4];
+        const float ciou = ciou_with_grad(pb, tb, g4);
+        acc_box += (1.0f - ciou) * wgt;
+        acc_dfl += ce * 0.25f * wgt;                                                  // mean over 4 sides (:324) * weight
+        const float kb = -(P.hyp_box * P.batch * inv_tss) * wgt;                      // L = (1-ciou)*w/tss
+        // d/d(dist): x1 = gx - d0 -> -g4[0]; y1 -> -g4[1]; x2 = gx + d2 -> g4[2]; y2 -> g4[3]
+        gd[0] = kb * -g4[0]; gd[1] = kb * -g4[1]; gd[2] = kb * g4[2]; gd[3] = kb * g4[3];
+        cdfl = P.hyp_dfl * P.batch * inv_tss * 0.25f * wgt;
+    }
+    if (WRITE_GRAD) {
+#pragma unroll 1
+        for (int s = 0; s < 4; ++s) {
+            // g_j = p_j * (gd*(j - d) + cdfl) - cdfl * ([j == tl] * wl + [j == tl+1] * wr)
+            const float gds = sel4(gd, s), m2s = sel4(m2, s), invs = sel4(inv_s, s), wls = sel4(wl, s);
+            const int tls = sel4(tl, s);
+            const float k0 = fmaf(-gds, sel4(dd, s), cdfl);
+            const float wr = 1.0f - wls;
+            float z[16];
+            if (fg) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) z[j] = __ldg(xin + (size_t)(s * 16 + j) * hw);
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                float gval = 0.f;
+                if (fg) {
+                    const float pj = ex2_fast(fmaf(z[j], kLog2e, -m2s)) * invs;
+                    const float tj = (j == tls) ? wls : ((j == tls + 1) ? wr : 0.f);
+                    gval = fmaf(-cdfl, tj, pj * fmaf(gds, (float)j, k0));
+                }
+                if (live) gout[(size_t)(s * 16 + j) * hw] = gval;
+            }
+        }
+    }
+}
 
-    const int b = blockIdx.y;
-    const int chunk = blockIdx.x;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-
+template <bool WRITE_GRAD>
+__device__ __forceinline__ void loss_cls_item(const LevelSet &L, const LossParams &P, int b, int chunk, int group,
+                                              int lane, float inv_tss, float &acc_cls) {
     int l = 0;
 #pragma unroll
     for (int k = 1; k < YS_MAX_LEVELS; ++k)
         if (k < L.n && chunk >= L.chunk_off[k]) l = k;
-    const int hw = L.hw[l], w = L.w[l];
-    const float st = L.stride[l];
-    const int i0 = (chunk - L.chunk_off[l]) * kChunk + lane * 4;   // first of this thread's 4 anchors (within level)
-    const bool live = i0 < hw;                                     // hw % 4 == 0 => all 4 anchors live together
-    const size_t img = (size_t)b * L.C * hw;
-    const float *xin = L.x[l] + img + i0;
-    float *gout = WRITE_GRAD ? (L.g[l] + img + i0) : nullptr;
-    const int a0 = L.a_off[l] + i0;
-
-    const float tss = P.tss[0];
-    const float inv_tss = 1.0f / tss;
-
-    int tg[4] = {-1, -1, -1, -1};
-    float nr[4] = {0.f, 0.f, 0.f, 0.f};
-    int lab[4] = {-1, -1, -1, -1};
-    if (live) {
-        int4 t4 = *reinterpret_cast<const int4 *>(P.tgi + (size_t)b * L.A + a0);
-        float4 n4 = *reinterpret_cast<const float4 *>(P.norm + (size_t)b * L.A + a0);
-        tg[0] = t4.x; tg[1] = t4.y; tg[2] = t4.z; tg[3] = t4.w;
-        nr[0] = n4.x; nr[1] = n4.y; nr[2] = n4.z; nr[3] = n4.w;
-    }
-    const int g0 = P.gt_off[b];
-    const bool any_fg = (tg[0] >= 0) | (tg[1] >= 0) | (tg[2] >= 0) | (tg[3] >= 0);
+    const int hw = L.hw[l];
+    const int i0 = (chunk - L.chunk_off[l]) * kChunk + lane * 4;    // hw % 4 == 0 => the 4 anchors are live together
+    if (i0 >= hw) return;
+    const int c_lo = group * kClsGroup;
+    const int c_n = min(kClsGroup, P.nc - c_lo);
+    const size_t off = ((size_t)b * L.C + 64 + c_lo) * hw + i0;
+    const float *xc = L.x[l] + off;
+    float *gc = WRITE_GRAD ? L.g[l] + off : nullptr;
+    const size_t arow = (size_t)b * L.A + L.a_off[l] + i0;
+    const int4 lab4 = __ldg(reinterpret_cast<const int4 *>(P.lab + arow));
+    const float4 nr4 = __ldg(reinterpret_cast<const float4 *>(P.norm + arow));
+    // the class of anchor k relative to this item's first channel (never matches when background: lab = -1)
+    const int r0 = lab4.x - c_lo, r1 = lab4.y - c_lo, r2 = lab4.z - c_lo, r3 = lab4.w - c_lo;
+    const float gscale = P.hyp_cls * P.batch * inv_tss;
+    float acc = 0.f;
+    auto one = [&](const float4 xv, int c) -> float4 {
+        float4 o;
+        float ls, sg, t;
+        t = (c == r0) ? nr4.x : 0.f; bce_logits(xv.x, t, ls, sg); acc += ls; o.x = (sg - t) * gscale;
+        t = (c == r1) ? nr4.y : 0.f; bce_logits(xv.y, t, ls, sg); acc += ls; o.y = (sg - t) * gscale;
+        t = (c == r2) ? nr4.z : 0.f; bce_logits(xv.z, t, ls, sg); acc += ls; o.z = (sg - t) * gscale;
+        t = (c == r3) ? nr4.w : 0.f; bce_logits(xv.w, t, ls, sg); acc += ls; o.w = (sg - t) * gscale;
+        return o;
+    };
+    if (c_n == kClsGroup) {
+#pragma unroll 1
+        for (int h = 0; h < kClsGroup; h += kClsBatch) {
+            float4 xv[kClsBatch];
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
-        if (tg[k] >= 0) lab[k] = P.gt_label[g0 + tg[k]];
-
-    float acc_box = 0.f, acc_cls = 0.f, acc_dfl = 0.f;
-
-    // ------------------------------------------------------------------ box side `warp`
-    // z[j][k]: logit of bin j for anchor k; becomes the softmax probability in place.
-    float4 z[16];
-    float dmine[4] = {0.f, 0.f, 0.f, 0.f}, lse[4] = {0.f, 0.f, 0.f, 0.f};
-    const int cbox = warp * 16;
-    if (any_fg) {
+            for (int u = 0; u < kClsBatch; ++u) xv[u] = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)(h + u) * hw));
 #pragma unroll
-        for (int j = 0; j < 16; ++j) z[j] = __ldg(reinterpret_cast<const float4 *>(xin + (size_t)(cbox + j) * hw));
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            float zz[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) zz[j] = (&z[j].x)[k];
-            float m, es;
-            dmine[k] = dfl_expect16(zz, m, es);
-            lse[k] = m + logf(es);
-            // keep raw logits in z for the cross-entropy lookups; probabilities are recomputed below
-        }
-    }
-    *reinterpret_cast<float4 *>(&s_d[warp][lane * 4]) = make_float4(dmine[0], dmine[1], dmine[2], dmine[3]);
-    __syncthreads();
-
-    if (any_fg) {
-        float4 d0 = *reinterpret_cast<const float4 *>(&s_d[0][lane * 4]);
-        float4 d1 = *reinterpret_cast<const float4 *>(&s_d[1][lane * 4]);
-        float4 d2 = *reinterpret_cast<const float4 *>(&s_d[2][lane * 4]);
-        float4 d3 = *reinterpret_cast<const float4 *>(&s_d[3][lane * 4]);
-        float gd[4];      // d(total)/d(dmine[k]) from the CIoU term
-        float cdfl[4];    // DFL gradient scale per anchor
-        int tl[4];
-        float wl[4], wr[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            gd[k] = 0.f; cdfl[k] = 0.f; tl[k] = 0; wl[k] = 0.f; wr[k] = 0.f;
-            if (tg[k] < 0) continue;
-            const int i = i0 + k;
-            const int iy = i / w, ix = i - iy * w;
-            const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
-            const float dd0 = (&d0.x)[k], dd1 = (&d1.x)[k], dd2 = (&d2.x)[k], dd3 = (&d3.x)[k];
-            const float4 pb = make_float4(gx - dd0, gy - dd1, gx + dd2, gy + dd3);       // grid units
-            const float4 q = __ldg(P.gt_box + g0 + tg[k]);
-            const float4 tb = make_float4(q.x / st, q.y / st, q.z / st, q.w / st);      // target_bboxes /= stride (:479)
-            float g4[4];
-            const float ciou = ciou_with_grad(pb, tb, g4);
-            const float wgt = nr[k];                                                    // target_scores.sum(-1) (:298)
-            if (warp == 0) acc_box += (1.0f - ciou) * wgt;
-            // d/d(dist): x1 = gx - d0 -> -g4[0]; y1 -> -g4[1]; x2 = gx + d2 -> g4[2]; y2 -> g4[3]
-            const float dsign = (warp == 0) ? -g4[0] : (warp == 1) ? -g4[1] : (warp == 2) ? g4[2] : g4[3];
-            gd[k] = -(P.hyp_box * P.batch * inv_tss) * wgt * dsign;                     // L = (1-ciou)*w/tss
-            // DFL target for my side (:304, :327-330, :315)
-            float t = (warp == 0) ? gx - tb.x : (warp == 1) ? gy - tb.y : (warp == 2) ? tb.z - gx : tb.w - gy;
-            t = fminf(fmaxf(t, 0.f), 14.99f);   // reg_max - 1 - 0.01
-            const int tli = (int)t;
-            tl[k] = tli;
-            wl[k] = (float)(tli + 1) - t;
-            wr[k] = 1.0f - wl[k];
-            float zl = 0.f, zr = 0.f;
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const float v = (&z[j].x)[k];
-                zl = (j == tli) ? v : zl;
-                zr = (j == tli + 1) ? v : zr;
-            }
-            const float ce = (lse[k] - zl) * wl[k] + (lse[k] - zr) * wr[k];
-            acc_dfl += ce * 0.25f * wgt;                                                // mean over 4 sides (:324) * weight
-            cdfl[k] = P.hyp_dfl * P.batch * inv_tss * 0.25f * wgt;
-        }
-        if (WRITE_GRAD) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                float4 o;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    float gval = 0.f;
-                    if (tg[k] >= 0) {
-                        const float p = expf((&z[j].x)[k] - lse[k]);
-                        gval = gd[k] * p * ((float)j - dmine[k]) +
-                               cdfl[k] * (p * (wl[k] + wr[k]) - (j == tl[k] ? wl[k] : 0.f) - (j == tl[k] + 1 ? wr[k] : 0.f));
-                    }
-                    (&o.x)[k] = gval;
-                }
-                *reinterpret_cast<float4 *>(gout + (size_t)(cbox + j) * hw) = o;
+            for (int u = 0; u < kClsBatch; ++u) {
+                const float4 o = one(xv[u], h + u);
+                if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)(h + u) * hw) = o;
             }
         }
-    } else if (WRITE_GRAD && live) {
-        const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int j = 0; j < 16; ++j) *reinterpret_cast<float4 *>(gout + (size_t)(cbox + j) * hw) = zero;
-    }
-
-    // ------------------------------------------------------------------ class channels of this warp
-    if (live) {
-        const int per = (P.nc + 3) >> 2;
-        const int c_lo = warp * per, c_hi = min(P.nc, c_lo + per);
-        const float gscale = P.hyp_cls * P.batch * inv_tss;
-        const float *xc = xin + (size_t)64 * hw;
-        float *gc = WRITE_GRAD ? gout + (size_t)64 * hw : nullptr;
-#pragma unroll 4
-        for (int c = c_lo; c < c_hi; ++c) {
+    } else {
+        for (int c = 0; c < c_n; ++c) {
             const float4 xv = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)c * hw));
-            float4 o;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float t = (c == lab[k]) ? nr[k] : 0.f;
-                float ls, sg;
-                bce_logits((&xv.x)[k], t, ls, sg);
-                acc_cls += ls;
-                (&o.x)[k] = (sg - t) * gscale;
-            }
+            const float4 o = one(xv, c);
             if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)c * hw) = o;
         }
     }
+    acc_cls += acc;
+}
 
+template <bool WRITE_GRAD>
+__global__ void __launch_bounds__(kLossThreads, 4) k_loss(LevelSet L, LossParams P) {
+    __shared__ float s_sum[kLossWarps][3];
+    __shared__ double s_fin[kLossWarps][3];
+    __shared__ int s_last;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int item = blockIdx.x * kLossWarps + warp;
+    const float inv_tss = 1.0f / P.tss[0];
+    float acc_box = 0.f, acc_cls = 0.f, acc_dfl = 0.f;
+    if (item < P.total_items) {
+        const int b = item / P.items_per_img;
+        const int r = item - b * P.items_per_img;
+        if (r < L.n_segs) {
+            loss_box_segment<WRITE_GRAD>(L, P, b, r, lane, inv_tss, acc_box, acc_dfl);
+        } else {
+            const int q = r - L.n_segs;
+            const int chunk = q / P.n_groups;
+            loss_cls_item<WRITE_GRAD>(L, P, b, chunk, q - chunk * P.n_groups, lane, inv_tss, acc_cls);
+        }
+    }
     // ------------------------------------------------------------------ block partial sums (fixed order)
     acc_box = warp_sum(acc_box);
     acc_cls = warp_sum(acc_cls);
@@ -316,39 +353,39 @@ __global__ void __launch_bounds__(kLossThreads) k_loss_fwd_bwd(LevelSet L, LossP
     if (lane == 0) { s_sum[warp][0] = acc_box; s_sum[warp][1] = acc_cls; s_sum[warp][2] = acc_dfl; }
     __syncthreads();
     if (tid == 0) {
-        float *o = P.partials + ((size_t)b * gridDim.x + chunk) * 4;
-        o[0] = s_sum[0][0] + s_sum[1][0] + s_sum[2][0] + s_sum[3][0];
-        o[1] = s_sum[0][1] + s_sum[1][1] + s_sum[2][1] + s_sum[3][1];
-        o[2] = s_sum[0][2] + s_sum[1][2] + s_sum[2][2] + s_sum[3][2];
-        o[3] = 0.f;
+        float t0 = 0.f, t1 = 0.f, t2 = 0.f;
+#pragma unroll
+        for (int w = 0; w < kLossWarps; ++w) { t0 += s_sum[w][0]; t1 += s_sum[w][1]; t2 += s_sum[w][2]; }
+        P.partials[blockIdx.x] = make_float4(t0, t1, t2, 0.f);
+        __threadfence();
+        const unsigned prev = atomicAdd(P.done, 1u);
+        s_last = (prev == gridDim.x - 1u);
     }
-}
-
-__global__ void __launch_bounds__(1024)
-k_loss_finalize(const float *__restrict__ partials, int n, const float *__restrict__ tss, float hyp_box, float hyp_cls,
-                float hyp_dfl, float batch, float *__restrict__ loss_out) {
-    __shared__ double s[32][3];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __syncthreads();
+    if (!s_last) return;
+    // ------------------------------------------------------------------ last block: ordered fp64 reduction
+    __threadfence();
     double a0 = 0, a1 = 0, a2 = 0;
-    for (int i = tid; i < n; i += 1024) {
-        const float4 v = reinterpret_cast<const float4 *>(partials)[i];
+    for (int i = tid; i < (int)gridDim.x; i += kLossThreads) {
+        const float4 v = __ldcg(P.partials + i);
         a0 += v.x; a1 += v.y; a2 += v.z;
     }
     a0 = warp_sum(a0); a1 = warp_sum(a1); a2 = warp_sum(a2);
-    if (lane == 0) { s[warp][0] = a0; s[warp][1] = a1; s[warp][2] = a2; }
+    if (lane == 0) { s_fin[warp][0] = a0; s_fin[warp][1] = a1; s_fin[warp][2] = a2; }
     __syncthreads();
     if (tid == 0) {
         double t0 = 0, t1 = 0, t2 = 0;
-        for (int w = 0; w < 32; ++w) { t0 += s[w][0]; t1 += s[w][1]; t2 += s[w][2]; }
-        const double inv = 1.0 / (double)tss[0];
+        for (int w = 0; w < kLossWarps; ++w) { t0 += s_fin[w][0]; t1 += s_fin[w][1]; t2 += s_fin[w][2]; }
+        const double inv = 1.0 / (double)P.tss[0];
         // loss[0] = box/tss*hyp_box, loss[1] = cls/tss*hyp_cls, loss[2] = dfl/tss*hyp_dfl (:475, :300, :306, :495-497)
-        const float lb = (float)(t0 * inv) * hyp_box;
-        const float lc = (float)(t1 * inv) * hyp_cls;
-        const float ld = (float)(t2 * inv) * hyp_dfl;
-        loss_out[0] = (lb + lc + ld) * batch;   // loss.sum() * batch_size (:499)
-        loss_out[1] = lb;
-        loss_out[2] = lc;
-        loss_out[3] = ld;
+        const float lb = (float)(t0 * inv) * P.hyp_box;
+        const float lc = (float)(t1 * inv) * P.hyp_cls;
+        const float ld = (float)(t2 * inv) * P.hyp_dfl;
+        P.loss_out[0] = (lb + lc + ld) * P.batch;   // loss.sum() * batch_size (:499)
+        P.loss_out[1] = lb;
+        P.loss_out[2] = lc;
+        P.loss_out[3] = ld;
+        *P.done = 0u;
     }
 }
 
@@ -393,11 +430,13 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
     YS_REQUIRE(nc >= 1, YS_ERR_BAD_ARG, "nc must be >= 1");
     L.n = n_levels;
     L.C = 4 * reg_max + nc;
-    int a = 0, ch = 0;
+    int a = 0, ch = 0, sg = 0;
     for (int i = 0; i < n_levels; ++i) {
         YS_REQUIRE(xs[i] != nullptr && hs[i] > 0 && ws[i] > 0, YS_ERR_BAD_ARG, "level %d: null pointer or empty shape", i);
         YS_REQUIRE(((uintptr_t)xs[i] & 15) == 0, YS_ERR_BAD_ARG, "level %d: pointer must be 16-byte aligned", i);
         YS_REQUIRE((hs[i] * ws[i]) % 4 == 0, YS_ERR_UNSUPPORTED, "level %d: h*w must be a multiple of 4 (float4 path)", i);
+        L.seg_off[i] = sg;
+        sg += (hs[i] * ws[i] + kSeg - 1) / kSeg;
         L.x[i] = xs[i];
         L.g[i] = gs ? gs[i] : nullptr;
         if (gs) YS_REQUIRE(gs[i] != nullptr && ((uintptr_t)gs[i] & 15) == 0, YS_ERR_BAD_ARG, "level %d: bad grad pointer", i);
@@ -409,28 +448,34 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
         a += L.hw[i];
         ch += (L.hw[i] + kChunk - 1) / kChunk;
     }
-    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.chunk_off[i] = ch; }
+    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.chunk_off[i] = ch; L.seg_off[i] = sg; }
     for (int i = n_levels; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; }
     L.A = a;
     L.n_chunks = ch;
+    L.n_segs = sg;
     return YS_OK;
 }
 
 struct LossWorkspace {
-    int *gt_off, *rank, *cursor, *gt_label, *owned_cnt, *gt_flags, *forced, *tgi;
-    float4 *gt_box, *pbox;
+    int *gt_off, *rank, *cursor, *gt_label, *owned_cnt, *gt_flags, *forced, *tgi, *lab;
+    float4 *gt_box, *pbox, *partials;
     unsigned long long *best_key;
-    float *norm, *tss, *partials;
+    float *norm, *tss, *scan_partial;
     double *img_sum;
-    unsigned *done_counter;
+    unsigned *counters;      // [0] images finished (k_assign), [1] blocks finished (k_loss), [2 + b] blocks of image b finished
     size_t bytes;
 };
 
-static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, int n_gt) {
+static inline int scan_blocks(int A) { return (A + kScanThreads - 1) / kScanThreads; }
+static inline size_t loss_items_bound(int B, int A, int nc) {
+    const size_t per_img = (size_t)A / kSeg + YS_MAX_LEVELS + ((size_t)A / kChunk + YS_MAX_LEVELS) * ((nc + kClsGroup - 1) / kClsGroup);
+    return (size_t)B * per_img;
+}
+
+static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, int n_gt, int nc) {
     Carver c(base, cap);
     const size_t N = (size_t)(n_gt > 0 ? n_gt : 1);
-    const size_t chunks = (size_t)B * ((size_t)(A + kChunk - 1) / kChunk + YS_MAX_LEVELS);
-    W.done_counter = c.take<unsigned>(64);        // zeroed once by the caller's first memset; self-resetting
+    W.counters = c.take<unsigned>((size_t)B + 2);
     W.tss = c.take<float>(64);
     W.gt_off = c.take<int>((size_t)B + 1);
     W.cursor = c.take<int>((size_t)B + 1);
@@ -442,10 +487,12 @@ static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, i
     W.gt_box = c.take<float4>(N);
     W.best_key = c.take<unsigned long long>(N);
     W.img_sum = c.take<double>((size_t)B);
+    W.scan_partial = c.take<float>((size_t)B * scan_blocks(A));
     W.tgi = c.take<int>((size_t)B * A);
+    W.lab = c.take<int>((size_t)B * A);
     W.norm = c.take<float>((size_t)B * A);
     W.pbox = c.take<float4>((size_t)B * A);
-    W.partials = c.take<float>(chunks * 4);
+    W.partials = c.take<float4>(loss_items_bound(B, A, nc) / kLossWarps + 2);
     W.bytes = align_up(c.off, 256);
 }
 
@@ -453,9 +500,9 @@ static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, i
 
 using namespace ys;
 
-extern "C" size_t ys_detection_loss_workspace_bytes(int B, int A, int n_gt) {
+extern "C" size_t ys_detection_loss_workspace_bytes(int B, int A, int n_gt, int nc) {
     LossWorkspace W;
-    carve_loss(W, nullptr, 0, B > 0 ? B : 1, A > 0 ? A : 1, n_gt);
+    carve_loss(W, nullptr, 0, B > 0 ? B : 1, A > 0 ? A : 1, n_gt, nc > 0 ? nc : 1);
     return W.bytes;
 }
 
@@ -477,7 +524,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     int rc = build_levels(L, n_levels, level_x_host, level_grad_host, level_h_host, level_w_host, level_stride_host, nc, reg_max);
     if (rc) return rc;
     LossWorkspace W;
-    carve_loss(W, workspace, workspace_bytes, B, L.A, n_gt);
+    carve_loss(W, workspace, workspace_bytes, B, L.A, n_gt, nc);
     YS_REQUIRE(W.bytes <= workspace_bytes, YS_ERR_WORKSPACE, "workspace too small: need %zu, got %zu", W.bytes, workspace_bytes);
     YS_REQUIRE(((uintptr_t)workspace & 255) == 0, YS_ERR_BAD_ARG, "workspace must be 256-byte aligned");
     if (pred_boxes_px) { YS_REQUIRE(((uintptr_t)pred_boxes_px & 15) == 0, YS_ERR_BAD_ARG, "pred_boxes_px must be 16-byte aligned"); }
@@ -486,10 +533,10 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
 
     if (stages == 0) stages = YS_STAGE_ALL;
     if (stages & YS_STAGE_PACK) {
-        cudaMemsetAsync(W.done_counter, 0, sizeof(unsigned), stream);
         k_pack_gt<<<1, kPackThreads, 0, stream>>>((const long long *)batch_idx, (const long long *)cls,
                                                   (const float4 *)bboxes, n_gt, B, nc, scale_x, scale_y, W.gt_off, W.rank,
-                                                  W.cursor, W.gt_box, W.gt_label, W.best_key, W.owned_cnt, W.gt_flags);
+                                                  W.cursor, W.gt_box, W.gt_label, W.best_key, W.owned_cnt, W.gt_flags,
+                                                  W.counters, B + 2);
         YS_CHECK_LAUNCH("k_pack_gt");
     }
 
@@ -499,35 +546,33 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags; io.forced = W.forced;
     io.pbox = pred_boxes_px ? (float4 *)pred_boxes_px : W.pbox;
     io.tgi = target_gt_idx ? (int *)target_gt_idx : W.tgi;
+    io.lab = W.lab;
     io.norm = norm_out ? norm_out : W.norm;
-    io.img_sum = W.img_sum; io.tss = W.tss; io.done_counter = W.done_counter;
+    io.partial = W.scan_partial; io.img_sum = W.img_sum; io.tss = W.tss;
+    io.done_counter = W.counters; io.img_done = W.counters + 2;
     io.nc = nc; io.alpha = alpha; io.beta = beta; io.eps = 1e-9f;
 
-    dim3 gs((L.A + kScanThreads - 1) / kScanThreads, B);
-    if (stages & YS_STAGE_SCAN) {
-        k_assign_scan<true><<<gs, kScanThreads, 0, stream>>>(L, io);
-        YS_CHECK_LAUNCH("k_assign_scan");
-    }
-    if (stages & YS_STAGE_FIXUP) {
-        k_assign_fixup<true><<<B, kFixThreads, 0, stream>>>(L, io, B);
-        YS_CHECK_LAUNCH("k_assign_fixup");
+    if (stages & YS_STAGE_ASSIGN) {
+        dim3 gs(scan_blocks(L.A), B);
+        k_assign<true><<<gs, kScanThreads, 0, stream>>>(L, io, B);
+        YS_CHECK_LAUNCH("k_assign");
     }
 
-    LossParams P;
-    P.tgi = io.tgi; P.norm = io.norm; P.gt_off = W.gt_off; P.gt_box = W.gt_box; P.gt_label = W.gt_label;
-    P.tss = W.tss; P.partials = W.partials; P.nc = nc;
-    P.hyp_box = hyp_box; P.hyp_cls = hyp_cls; P.hyp_dfl = hyp_dfl; P.batch = (float)B;
-    dim3 gl(L.n_chunks, B);
     if (stages & YS_STAGE_LOSS) {
+        LossParams P;
+        P.tgi = io.tgi; P.lab = W.lab; P.norm = io.norm; P.gt_off = W.gt_off; P.gt_box = W.gt_box;
+        P.tss = W.tss; P.partials = W.partials; P.done = W.counters + 1; P.loss_out = loss_out;
+        P.nc = nc; P.n_groups = (nc + kClsGroup - 1) / kClsGroup;
+        P.items_per_img = L.n_segs + L.n_chunks * P.n_groups;
+        P.total_items = B * P.items_per_img;
+        P.hyp_box = hyp_box; P.hyp_cls = hyp_cls; P.hyp_dfl = hyp_dfl; P.batch = (float)B;
+        YS_REQUIRE((long long)B * P.items_per_img < 2147483647LL, YS_ERR_UNSUPPORTED, "too many work items");
+        const unsigned blocks = (unsigned)((P.total_items + kLossWarps - 1) / kLossWarps);
         if (level_grad_host)
-            k_loss_fwd_bwd<true><<<gl, kLossThreads, 0, stream>>>(L, P);
+            k_loss<true><<<blocks, kLossThreads, 0, stream>>>(L, P);
         else
-            k_loss_fwd_bwd<false><<<gl, kLossThreads, 0, stream>>>(L, P);
-        YS_CHECK_LAUNCH("k_loss_fwd_bwd");
-    }
-    if (stages & YS_STAGE_FINAL) {
-        k_loss_finalize<<<1, 1024, 0, stream>>>(W.partials, L.n_chunks * B, W.tss, hyp_box, hyp_cls, hyp_dfl, (float)B, loss_out);
-        YS_CHECK_LAUNCH("k_loss_finalize");
+            k_loss<false><<<blocks, kLossThreads, 0, stream>>>(L, P);
+        YS_CHECK_LAUNCH("k_loss");
     }
     return YS_OK;
 }
@@ -549,23 +594,24 @@ namespace ys {
 struct AssignWorkspace {
     int *owned_cnt, *gt_flags, *forced, *tgi;
     unsigned long long *best_key;
-    float *norm, *tss;
+    float *norm, *tss, *scan_partial;
     double *img_sum;
-    unsigned *done_counter;
+    unsigned *counters;  // [0] images finished, [2 + b] blocks of image b finished
     size_t zero_bytes;   // leading region that must be zeroed per call
     size_t bytes;
 };
 static void carve_assign(AssignWorkspace &W, void *base, size_t cap, int B, int A, int G) {
     Carver c(base, cap);
     const size_t N = (size_t)B * G;
-    W.done_counter = c.take<unsigned>(64);
+    W.counters = c.take<unsigned>((size_t)B + 2);
     W.owned_cnt = c.take<int>(N);
     W.gt_flags = c.take<int>(N);
-    W.best_key = c.take<unsigned long long>(N);
     W.zero_bytes = align_up(c.off, 256);
+    W.best_key = c.take<unsigned long long>(N);
     W.tss = c.take<float>(64);
     W.forced = c.take<int>(2 * N);
     W.img_sum = c.take<double>((size_t)B);
+    W.scan_partial = c.take<float>((size_t)B * scan_blocks(A));
     W.tgi = c.take<int>((size_t)B * A);
     W.norm = c.take<float>((size_t)B * A);
     W.bytes = align_up(c.off, 256);
@@ -599,21 +645,21 @@ extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, co
     LevelSet L;
     L.n = 1; L.A = A; L.C = nc; L.n_chunks = 0;
     for (int i = 0; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; }
-    for (int i = 0; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = i == 0 ? 0 : A; L.chunk_off[i] = 0; }
+    for (int i = 0; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = i == 0 ? 0 : A; L.chunk_off[i] = 0; L.seg_off[i] = 0; }
+    L.n_segs = 0;
 
     AssignIO io;
     io.gt_off = nullptr; io.G = G; io.gt_box = (const float4 *)gt_bboxes; io.gt_label_i = nullptr;
     io.gt_label_f = gt_labels; io.gt_valid = mask_gt; io.pd_box = (const float4 *)pd_bboxes; io.pd_scores = pd_scores;
     io.anc = (const float2 *)anc_points; io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags;
-    io.forced = W.forced; io.pbox = nullptr; io.tgi = W.tgi; io.norm = norm_out ? norm_out : W.norm;
-    io.img_sum = W.img_sum; io.tss = W.tss; io.done_counter = W.done_counter;
+    io.forced = W.forced; io.pbox = nullptr; io.tgi = W.tgi; io.lab = nullptr; io.norm = norm_out ? norm_out : W.norm;
+    io.partial = W.scan_partial; io.img_sum = W.img_sum; io.tss = W.tss;
+    io.done_counter = W.counters; io.img_done = W.counters + 2;
     io.nc = nc; io.alpha = alpha; io.beta = beta; io.eps = eps;
 
-    dim3 gs((A + kScanThreads - 1) / kScanThreads, B);
-    k_assign_scan<false><<<gs, kScanThreads, 0, stream>>>(L, io);
-    YS_CHECK_LAUNCH("k_assign_scan(dense)");
-    k_assign_fixup<false><<<B, kFixThreads, 0, stream>>>(L, io, B);
-    YS_CHECK_LAUNCH("k_assign_fixup(dense)");
+    dim3 gs(scan_blocks(A), B);
+    k_assign<false><<<gs, kScanThreads, 0, stream>>>(L, io, B);
+    YS_CHECK_LAUNCH("k_assign(dense)");
     const size_t tot = (size_t)B * A;
     k_assign_emit<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(B, A, G, nc, W.tgi, io.norm, gt_labels,
                                                                    (const float4 *)gt_bboxes, target_labels,

@@ -161,13 +161,72 @@ YS_HD float ciou_with_grad(float4 p, float4 t, float g[4]) {
     return ciou;
 }
 
+// ---------------------------------------------------------------------------
+// Fast transcendental building blocks of the tolerance section.  Device: one MUFU each
+// (ex2.approx / rcp.approx, ~2^-22 relative error); host: libm, for the CPU unit tests.
+// ---------------------------------------------------------------------------
+constexpr float kLog2e = 1.4426950408889634f;
+
+YS_HD float ex2_fast(float a) {
+#ifdef __CUDA_ARCH__
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r;
+#else
+    return exp2f(a);
+#endif
+}
+YS_HD float rcp_fast(float a) {
+#ifdef __CUDA_ARCH__
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r;
+#else
+    return 1.0f / a;
+#endif
+}
+
+// log1p(e)/e on e in [0,1]: degree-7 minimax polynomial (Lawson fit; max relative error of e*P(e) vs log1p(e)
+// 3.7e-7 in fp32 Horner form, -1.6e-7 as e -> 0).  No MUFU, no branch.
+YS_HD float log1p_over_e(float e) {
+    float p = -8.783297754e-03f;
+    p = fmaf(p, e, 4.494444638e-02f);
+    p = fmaf(p, e, -1.088579088e-01f);
+    p = fmaf(p, e, 1.782550513e-01f);
+    p = fmaf(p, e, -2.452358495e-01f);
+    p = fmaf(p, e, 3.328017316e-01f);
+    p = fmaf(p, e, -4.999769926e-01f);
+    p = fmaf(p, e, 9.999998357e-01f);
+    return p;
+}
+
 // Numerically stable BCE-with-logits and sigmoid sharing one exponential.
 // loss = max(x,0) - x*t + log1p(exp(-|x|)) ; sig = sigmoid(x)
 YS_HD void bce_logits(float x, float t, float &loss, float &sig) {
-    float e = expf(-fabsf(x));
-    float inv = 1.0f / (1.0f + e);
+    const float e = ex2_fast(fabsf(x) * -kLog2e);     // exp(-|x|) in (0,1]
+    const float inv = rcp_fast(1.0f + e);              // sigmoid(|x|)
     sig = x >= 0.f ? inv : e * inv;
-    loss = fmaxf(x, 0.f) - x * t + log1pf(e);
+    loss = fmaf(e, log1p_over_e(e), fmaf(-x, t, fmaxf(x, 0.f)));
+}
+
+// Softmax statistics of 16 logits in the exp2 domain: returns the expectation d = sum_j j*softmax(z)_j
+// (losses/yolo_v8_loss.py:534-536); m2 = max(z)*log2e and inv_s = 1/sum_j 2^(z_j*log2e - m2), so that
+// softmax(z)_j = ex2(z_j*log2e - m2) * inv_s and logsumexp(z) = (m2 + log2(sum)) * ln2.
+YS_HD float dfl_stats16(const float (&z)[16], float &m2, float &inv_s) {
+    float m = z[0];
+#pragma unroll
+    for (int j = 1; j < 16; ++j) m = fmaxf(m, z[j]);
+    const float mm = m * kLog2e;
+    float s = 0.f, d = 0.f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        const float e = ex2_fast(fmaf(z[j], kLog2e, -mm));
+        s += e;
+        d = fmaf(e, (float)j, d);
+    }
+    m2 = mm;
+    inv_s = 1.0f / s;
+    return d * inv_s;
 }
 
 }  // namespace ys

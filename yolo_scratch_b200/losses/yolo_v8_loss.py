@@ -196,7 +196,7 @@ class _FusedDetectionLoss(torch.autograd.Function):
         A = sum(x.shape[2] * x.shape[3] for x in xs)
         n_gt = int(batch_idx.shape[0])
         out = torch.empty(4, device=dev, dtype=torch.float32)
-        ws = owner._ws.get(lib.ys_detection_loss_workspace_bytes(B, A, n_gt), dev)
+        ws = owner._ws.get(lib.ys_detection_loss_workspace_bytes(B, A, n_gt, owner.nc), dev)
         pb = tgi = nrm = None
         if export:
             pb = torch.empty(B, A, 4, device=dev)
