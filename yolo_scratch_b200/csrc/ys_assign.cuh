@@ -20,7 +20,7 @@ namespace ys {
 
 constexpr int kScanThreads = 256;
 constexpr int kGtTile = 512;        // GT boxes staged per shared-memory tile
-constexpr int kFixSmemGt = 1024;    // per-image GT count the fix-up handles with shared-memory scratch
+constexpr int kFixSmemGt = 768;     // per-image GT count the fix-up handles with shared-memory scratch
 
 // Everything the assignment kernel needs to know about where boxes, scores and GT come from.
 struct AssignIO {
@@ -39,7 +39,7 @@ struct AssignIO {
     int *owned_cnt;
     int *gt_flags;              // 1: some anchor centre lies inside
     unsigned long long *best_key;   // fix-up scratch when an image has more than kFixSmemGt GT
-    int *forced;                // same: 2 ints per GT
+    int *forced;                // same: 8 ints per GT (forced x2, needy, kk, tg0, lost, spare x2)
     // per-anchor outputs (B,A)
     float4 *pbox;               // fused: decoded px boxes (written by the scan)
     int *tgi;                   // -1 = background
@@ -172,6 +172,9 @@ struct FixSmem {
     int cnt[kFixSmemGt];
     int forced[2 * kFixSmemGt];
     int needy[kFixSmemGt];
+    int kk[kFixSmemGt];
+    int tg0[kFixSmemGt];
+    int lost[kFixSmemGt];
 };
 union AssignSmem {
     ScanSmem s;
@@ -182,7 +185,7 @@ template <bool FUSED>
 __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, FixSmem &S, int nblk);
 
 template <bool FUSED>
-__global__ void __launch_bounds__(kScanThreads) k_assign(LevelSet L, AssignIO io, int B) {
+__global__ void __launch_bounds__(kScanThreads, 4) k_assign(LevelSet L, AssignIO io, int B) {
     __shared__ AssignSmem sm;
     __shared__ float s_red[kScanThreads / 32];
     __shared__ int s_flag;
@@ -336,27 +339,61 @@ __global__ void __launch_bounds__(kScanThreads) k_assign(LevelSet L, AssignIO io
 
 // ---------------------------------------------------------------------------------------------------
 // Fix-up of one image (all kScanThreads threads of the last block to finish that image).
+// Phases, separated by block barriers; everything that is parallel in the reference's semantics runs on all
+// eight warps, only the order-dependent bookkeeping of loop 2 is serial (one thread, shared-memory state):
+//   A  classify the GT: lonely (no anchor centre inside -> loop 1 fires) / ownerless (loop 2 may fire)
+//   B  arg-max over all anchors of IoU(anchor, GT) for those GT (block-wide, first maximum)
+//   1  first resolve (:142) of the anchors loop 1 forced, one warp per anchor
+//   B' (rare) arg-max for GT that lost their only anchor in phase 1
+//   2  loop 2 (:146-162), sequential in g.  Its tgi/fg edits are discarded by the final resolve (:165), so only
+//      the per-GT owner counts are tracked: gold = current owner of the stolen anchor.
+//   3  final resolve from mask_pos alone for every anchor carrying a forced entry, one warp per anchor
 // ---------------------------------------------------------------------------------------------------
 template <bool FUSED>
+__device__ __forceinline__ void fix_argmax(const LevelSet &L, const AssignIO &io, int b, int g0, const int *list,
+                                           int nn, unsigned long long *keyp) {
+    const int tid = threadIdx.x;
+    const float4 *pb = (FUSED ? io.pbox : io.pd_box) + (size_t)b * L.A;
+#pragma unroll 4
+    for (int a = tid; a < L.A; a += kScanThreads) {
+        const float4 p = FUSED ? __ldcg(pb + a) : pb[a];
+        const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
+        for (int q = 0; q < nn; ++q) {
+            const int j = list[q];
+            const float4 gq = io.gt_box[g0 + j];
+            const float ov = iou_assign_lazy(p, area_p, gq, area_eps_h(gq.x, gq.y, gq.z, gq.w));
+            const unsigned long long key = argmax_key(ov, (unsigned)a);
+            if (key > *((volatile unsigned long long *)&keyp[j])) atomicMax(&keyp[j], key);
+        }
+    }
+}
+
+template <bool FUSED>
 __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, FixSmem &S, int nblk) {
-    __shared__ int s_todo, s_nneedy;
-    __shared__ double s_delta;
+    __shared__ int s_nneedy, s_nlost, s_resume, s_nfired, s_want;
+    __shared__ double s_delta[kScanThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int kWarps = kScanThreads / 32;
     int g0, n;
     gt_range<FUSED>(io, b, g0, n);
     volatile int *tgi = io.tgi + (size_t)b * L.A;      // written by other blocks of this launch: no L1
     int *labp = io.lab ? io.lab + (size_t)b * L.A : nullptr;
     volatile float *norm = io.norm + (size_t)b * L.A;
-    // per-GT scratch: shared memory when the image's GT fit, else the global scratch in place
+    // per-GT scratch: shared memory when the image's GT fit, else the global scratch (8 ints per GT) in place
     const bool in_smem = n <= kFixSmemGt;
+    int *gs = io.forced + 8 * (size_t)g0;
     int *cntp = in_smem ? S.cnt : (io.owned_cnt + g0);
-    int *forced = in_smem ? S.forced : (io.forced + 2 * (size_t)g0);   // [2j] loop-1 anchor, [2j+1] loop-2 anchor
+    int *forced = in_smem ? S.forced : gs;                         // [2j] loop-1 anchor, [2j+1] loop-2 anchor
+    int *needy = in_smem ? S.needy : (gs + 2 * (size_t)n);         // GT whose arg-max anchor is needed
+    int *kk = in_smem ? S.kk : (gs + 3 * (size_t)n);               // arg-max anchor of GT j (-1: not computed)
+    int *tg0 = in_smem ? S.tg0 : (gs + 4 * (size_t)n);             // owner GT of anchor kk[j] after phase 1
+    int *lost = in_smem ? S.lost : (gs + 5 * (size_t)n);
     unsigned long long *keyp = in_smem ? S.key : (io.best_key + g0);
-    int *needy = in_smem ? S.needy : nullptr;
 
-    if (tid == 0) { s_todo = 0; s_nneedy = 0; s_delta = 0.0; }
+    if (tid == 0) { s_nneedy = 0; s_nlost = 0; }
+    if (tid < kWarps) s_delta[tid] = 0.0;
     __syncthreads();
-    // ---- which GT need a forced assignment?  (common case: none)
+    // ---- A: which GT need a forced assignment?  (common case: none)
     for (int j = tid; j < n; j += kScanThreads) {
         const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
         const int c = __ldcg(io.owned_cnt + g0 + j);
@@ -366,103 +403,117 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
         forced[2 * j] = lonely1 ? -2 : -1;               // -2: pending, resolved below
         forced[2 * j + 1] = -1;
         keyp[j] = 0ull;
-        if (valid && (lonely1 || c == 0)) {               // loop 2 (:146-162) can only fire for GT that own nothing now
-            s_todo = 1;
-            if (in_smem) needy[atomicAdd(&s_nneedy, 1)] = j;
-        }
+        kk[j] = -1;
+        if (valid && (lonely1 || c == 0))                // loop 2 (:146-162) can only fire for GT that own nothing now
+            needy[atomicAdd(&s_nneedy, 1)] = j;
     }
     __syncthreads();
-    if (s_todo) {
-        // -- arg-max over all anchors of IoU(anchor, GT j) (first maximum) for the GT that may need it (:136, :156)
-        const int nn = in_smem ? s_nneedy : n;
-        for (int a = tid; a < L.A; a += kScanThreads) {
-            const float4 p = FUSED ? __ldcg(io.pbox + (size_t)b * L.A + a) : io.pd_box[(size_t)b * L.A + a];
-            const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
-            for (int q = 0; q < nn; ++q) {
-                const int j = in_smem ? needy[q] : q;
-                const float4 gq = io.gt_box[g0 + j];
-                const float ov = iou_assign_lazy(p, area_p, gq, area_eps_h(gq.x, gq.y, gq.z, gq.w));
-                const unsigned long long key = argmax_key(ov, (unsigned)a);
-                if (key > *((volatile unsigned long long *)&keyp[j])) atomicMax(&keyp[j], key);
+    const int nneedy = s_nneedy;
+    if (nneedy > 0) {      // block-uniform
+        // ---- B: arg-max over all anchors of IoU(anchor, GT j), first maximum (:136, :156)
+        fix_argmax<FUSED>(L, io, b, g0, needy, nneedy, keyp);
+        __syncthreads();
+        for (int q = tid; q < nneedy; q += kScanThreads) {
+            const int j = needy[q];
+            const int k = (int)argmax_key_index(keyp[j]);
+            kk[j] = k;
+            if (forced[2 * j] == -2) forced[2 * j] = k;
+        }
+        __syncthreads();
+        // ---- 1: first resolve (:142) for the anchors loop 1 touched; everyone else keeps the scan's result
+        for (int q = warp; q < nneedy; q += kWarps) {
+            const int j = needy[q];
+            const int k = forced[2 * j];
+            if (k < 0) continue;
+            bool seen = false;   // k already handled through another lonely GT?  (lowest j owns the job)
+            for (int jj = lane; jj < n; jj += 32) seen |= (jj < j && forced[2 * jj] == k);
+            if (__any_sync(0xffffffffu, seen)) continue;
+            float ov;
+            const int gnew = resolve_row<FUSED>(io, L, b, k, g0, n, forced, false, ov);
+            if (lane == 0) {
+                const int gold = tgi[k];
+                if (gold >= 0) atomicSub(&cntp[gold], 1);
+                if (gnew >= 0) atomicAdd(&cntp[gnew], 1);
+                tgi[k] = gnew;
             }
         }
         __syncthreads();
-        for (int j = tid; j < n; j += kScanThreads)
-            if (forced[2 * j] == -2) forced[2 * j] = (int)argmax_key_index(keyp[j]);
+        // ---- B': GT that own nothing now but were not on the needy list (they lost their only anchor in phase 1)
+        for (int j = tid; j < n; j += kScanThreads) {
+            const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
+            if (valid && cntp[j] == 0 && kk[j] < 0) lost[atomicAdd(&s_nlost, 1)] = j;
+        }
         __syncthreads();
-        if (warp == 0) {
-            // -- first resolve (:142) for the anchors loop 1 touched; everyone else keeps the scan's result
-            for (int j = 0; j < n; ++j) {
-                const int k = forced[2 * j];
-                if (k < 0) continue;
-                bool seen = false;   // k already handled through an earlier GT?
-                for (int jj = lane; jj < j; jj += 32) seen |= (forced[2 * jj] == k);
-                if (__any_sync(0xffffffffu, seen)) continue;
-                float ov;
-                const int gnew = resolve_row<FUSED>(io, L, b, k, g0, n, forced, false, ov);
-                if (lane == 0) {
-                    const int gold = tgi[k];
+        const int nlost = s_nlost;
+        if (nlost > 0) {
+            fix_argmax<FUSED>(L, io, b, g0, lost, nlost, keyp);
+            __syncthreads();
+            for (int q = tid; q < nlost; q += kScanThreads) kk[lost[q]] = (int)argmax_key_index(keyp[lost[q]]);
+            __syncthreads();
+        }
+        // owner of every candidate anchor after phase 1
+        for (int j = tid; j < n; j += kScanThreads) tg0[j] = kk[j] >= 0 ? tgi[kk[j]] : -1;
+        __syncthreads();
+        // ---- 2: loop 2 (:146-162): sequential in g; later GT see the edits of earlier ones.  A GT whose only
+        //      anchor is stolen inside this loop has no arg-max yet: the serial thread stops there, the block
+        //      computes it, and the loop resumes at the same GT.
+        if (tid == 0) { s_resume = 0; s_nfired = 0; }
+        __syncthreads();
+        while (true) {
+            if (tid == 0) {
+                int nfired = s_nfired, want = -1;               // fired GT are remembered in lost[] (reused)
+                for (int j = s_resume; j < n; ++j) {
+                    const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
+                    if (!valid || cntp[j] != 0) continue;
+                    const int k = kk[j];
+                    if (k < 0) { want = j; s_resume = j; break; }
+                    int gold = tg0[j];
+                    for (int f = 0; f < nfired; ++f)
+                        if (kk[lost[f]] == k) gold = lost[f];   // stolen earlier in this loop: latest thief owns it
                     if (gold >= 0) cntp[gold] -= 1;
-                    if (gnew >= 0) cntp[gnew] += 1;
-                    tgi[k] = gnew;
-                }
-                __syncwarp();
-            }
-            // -- loop 2 (:146-162): sequential in g; later GT see the edits of earlier ones
-            for (int j = 0; j < n; ++j) {
-                const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
-                if (!valid || cntp[j] != 0) continue;              // warp-uniform (shared / L2 state, read after __syncwarp)
-                unsigned long long key = keyp[j];
-                if (key == 0ull) {
-                    // a GT that lost its only anchor in the first resolve: its arg-max was not precomputed
-                    const float4 gq = io.gt_box[g0 + j];
-                    const float area_q = area_eps_h(gq.x, gq.y, gq.z, gq.w);
-                    for (int a = lane; a < L.A; a += 32) {
-                        const float4 p = FUSED ? __ldcg(io.pbox + (size_t)b * L.A + a) : io.pd_box[(size_t)b * L.A + a];
-                        const float ov = iou_assign_lazy(p, area_eps_h(p.x, p.y, p.z, p.w), gq, area_q);
-                        const unsigned long long kk = argmax_key(ov, (unsigned)a);
-                        key = kk > key ? kk : key;
-                    }
-                    key = warp_max(key);
-                }
-                if (lane == 0) {
-                    const int k = (int)argmax_key_index(key);
-                    keyp[j] = key;
-                    forced[2 * j + 1] = k;
-                    const int gold = tgi[k];
-                    if (gold >= 0) cntp[gold] -= 1;
-                    tgi[k] = j;
                     cntp[j] += 1;
+                    forced[2 * j + 1] = k;
+                    lost[nfired++] = j;
                 }
-                __syncwarp();
+                s_nfired = nfired;
+                s_want = want;
             }
-            // -- final resolve (:165) from mask_pos alone, for every anchor that carries a forced entry
-            double delta = 0.0;
-            for (int j = 0; j < 2 * n; ++j) {
-                const int k = forced[j];
-                if (k < 0) continue;
-                bool seen = false;
-                for (int jj = lane; jj < j; jj += 32) seen |= (forced[jj] == k);
-                if (__any_sync(0xffffffffu, seen)) continue;
-                float ov;
-                const int gfin = resolve_row<FUSED>(io, L, b, k, g0, n, forced, true, ov);
-                if (lane == 0) {
-                    tgi[k] = gfin;
-                    float nrm = 0.f;
-                    int lb = -1;
-                    if (gfin >= 0) {
-                        lb = label_of<FUSED>(io, g0 + gfin);
-                        const float sc = score_at<FUSED>(io, L, b, k, lb);
-                        nrm = align_norm(sc, ov, io.alpha, io.beta, io.eps);
-                    }
-                    delta += (double)nrm - (double)norm[k];
-                    norm[k] = nrm;
-                    if (labp) labp[k] = lb;
-                }
-                __syncwarp();
+            __syncthreads();
+            if (s_want < 0) break;                              // block-uniform
+            fix_argmax<FUSED>(L, io, b, g0, &s_want, 1, keyp);
+            __syncthreads();
+            if (tid == 0) {
+                const int k = (int)argmax_key_index(keyp[s_want]);
+                kk[s_want] = k;
+                tg0[s_want] = tgi[k];                           // loop 2 itself never writes tgi
             }
-            if (lane == 0) s_delta = delta;
+            __syncthreads();
         }
+        // ---- 3: final resolve (:165) from mask_pos alone, for every anchor that carries a forced entry
+        double delta = 0.0;
+        for (int e = warp; e < 2 * n; e += kWarps) {
+            const int k = forced[e];
+            if (k < 0) continue;
+            bool seen = false;
+            for (int jj = lane; jj < e; jj += 32) seen |= (forced[jj] == k);
+            if (__any_sync(0xffffffffu, seen)) continue;
+            float ov;
+            const int gfin = resolve_row<FUSED>(io, L, b, k, g0, n, forced, true, ov);
+            if (lane == 0) {
+                tgi[k] = gfin;
+                float nrm = 0.f;
+                int lb = -1;
+                if (gfin >= 0) {
+                    lb = label_of<FUSED>(io, g0 + gfin);
+                    const float sc = score_at<FUSED>(io, L, b, k, lb);
+                    nrm = align_norm(sc, ov, io.alpha, io.beta, io.eps);
+                }
+                delta += (double)nrm - (double)norm[k];
+                norm[k] = nrm;
+                if (labp) labp[k] = lb;
+            }
+        }
+        if (lane == 0) s_delta[warp] = delta;
     }
     __syncthreads();
     // ---- leave the per-GT scratch zeroed for the next call
@@ -476,7 +527,10 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
         for (int i = lane; i < nblk; i += 32) acc += (double)__ldcg(io.partial + (size_t)b * nblk + i);
         acc = warp_sum(acc);
         if (lane == 0) {
-            io.img_sum[b] = acc + s_delta;
+            double dsum = 0.0;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) dsum += s_delta[w];
+            io.img_sum[b] = acc + dsum;
             io.img_done[b] = 0u;
             __threadfence();
             const unsigned prev = atomicAdd(io.done_counter, 1u);

@@ -161,6 +161,7 @@ struct LossParams {
     const float *norm;       // (B,A)
     const int *gt_off;       // (B+1)
     const float4 *gt_box;    // px
+    const float4 *pbox;      // (B,A) decoded boxes, px (written by k_assign)
     const float *tss;        // [0]
     float4 *partials;        // (gridDim.x): box, cls, dfl partial sums (unnormalised)
     unsigned *done;          // arrival counter, self-resetting
@@ -181,6 +182,21 @@ template <typename T> __device__ __forceinline__ void put4(T (&a)[4], int s, T v
     a[0] = s == 0 ? v : a[0]; a[1] = s == 1 ? v : a[1]; a[2] = s == 2 ? v : a[2]; a[3] = s == 3 ? v : a[3];
 }
 
+// Zero-fill the 64 box-gradient rows of one 32-anchor segment: 8 lanes per 128-byte row, 4 rows per instruction.
+__device__ __forceinline__ void zero_box_rows(float *g0, int hw, int i0, int lane) {
+    const int piece = (lane & 7) * 4, rsub = lane >> 3;
+    if (i0 + piece < hw) {     // hw % 4 == 0: the 4 anchors of a piece are live together
+        float *p = g0 + (size_t)rsub * hw + piece;
+        const size_t step = (size_t)4 * hw;
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+            *reinterpret_cast<float4 *>(p) = z4;
+            p += step;
+        }
+    }
+}
+
 template <bool WRITE_GRAD>
 __device__ __forceinline__ void loss_box_segment(const LevelSet &L, const LossParams &P, int b, int seg, int lane,
                                                  float inv_tss, float &acc_box, float &acc_dfl) {
@@ -190,87 +206,90 @@ __device__ __forceinline__ void loss_box_segment(const LevelSet &L, const LossPa
         if (k < L.n && seg >= L.seg_off[k]) l = k;
     const int hw = L.hw[l], w = L.w[l];
     const float st = L.stride[l];
-    const int i = (seg - L.seg_off[l]) * kSeg + lane;
+    const int i0 = (seg - L.seg_off[l]) * kSeg;
+    const int i = i0 + lane;
     const bool live = i < hw;
     const size_t img = (size_t)b * L.C * hw;
-    const float *xin = L.x[l] + img + i;
-    float *gout = WRITE_GRAD ? (L.g[l] + img + i) : nullptr;
-    const int tg = live ? __ldg(P.tgi + (size_t)b * L.A + L.a_off[l] + i) : -1;
+    const size_t arow = (size_t)b * L.A + L.a_off[l] + i;
+    const int tg = live ? __ldg(P.tgi + arow) : -1;
     const bool fg = tg >= 0;
     if (!__any_sync(0xffffffffu, fg)) {
-        if (WRITE_GRAD && live) {
-#pragma unroll 16
-            for (int c = 0; c < 64; ++c) gout[(size_t)c * hw] = 0.f;
-        }
+        if (WRITE_GRAD) zero_box_rows(L.g[l] + img + i0, hw, i0, lane);
         return;
     }
+    // ---- per-anchor scalars.  Background lanes keep gd = cdfl = 0, which makes every gradient they emit +0.
     float gd[4] = {0.f, 0.f, 0.f, 0.f};       // d(total)/d(d_s) from the CIoU term
-    float dd[4] = {0.f, 0.f, 0.f, 0.f};       // ltrb expectation
-    float m2[4] = {0.f, 0.f, 0.f, 0.f}, inv_s[4] = {1.f, 1.f, 1.f, 1.f};
-    float wl[4] = {0.f, 0.f, 0.f, 0.f};
-    int tl[4] = {0, 0, 0, 0};
-    float cdfl = 0.f;
+    float tt[4] = {0.f, 0.f, 0.f, 0.f};       // DFL targets (ltrb, grid units)
+    float cdfl = 0.f, wgt = 0.f;
     if (fg) {
-        const float wgt = __ldg(P.norm + (size_t)b * L.A + L.a_off[l] + i);           // target_scores.sum(-1) (:298)
+        wgt = __ldg(P.norm + arow);                                                   // target_scores.sum(-1) (:298)
         const float4 q = __ldg(P.gt_box + __ldg(P.gt_off + b) + tg);
         const float4 tb = make_float4(q.x / st, q.y / st, q.z / st, q.w / st);        // target_bboxes /= stride (:479)
+        const float4 pp = __ldg(P.pbox + arow);                                       // decoded by k_assign, pixels
+        const float4 pb = make_float4(pp.x / st, pp.y / st, pp.z / st, pp.w / st);    // back to grid units (:412)
         const int iy = i / w, ix = i - iy * w;
         const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
-        // DFL targets (:304, :327-330, :315)
-        float tt[4] = {gx - tb.x, gy - tb.y, tb.z - gx, tb.w - gy};
-        float ce = 0.f;
-#pragma unroll 1
-        for (int s = 0; s < 4; ++s) {
-            float z[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) z[j] = __ldg(xin + (size_t)(s * 16 + j) * hw);
-            float m2s, invs;
-            const float ds = dfl_stats16(z, m2s, invs);
-            const float t = fminf(fmaxf(sel4(tt, s), 0.f), 14.99f);                   // reg_max - 1 - 0.01
-            const int tli = (int)t;
-            const float wls = (float)(tli + 1) - t;
-            // cross-entropy at bins tl and tl+1: lse - z[bin]; lse = (m2 - log2(inv_s)) * ln2
-            const float lse = (m2s - log2f(invs)) * 0.69314718055994531f;
-            const float zl = __ldg(xin + (size_t)(s * 16 + tli) * hw);
-            const float zr = __ldg(xin + (size_t)(s * 16 + tli + 1) * hw);
-            ce += (lse - zl) * wls + (lse - zr) * (1.0f - wls);
-            put4(dd, s, ds); put4(m2, s, m2s); put4(inv_s, s, invs); put4(wl, s, wls); put4(tl, s, tli);
-        }
-        const float4 pb = make_float4(gx - dd[0], gy - dd[1], gx + dd[2], gy + dd[3]);   // grid units
+        tt[0] = gx - tb.x; tt[1] = gy - tb.y; tt[2] = tb.z - gx; tt[3] = tb.w - gy;   // bbox2dist (:304, :327-330)
         float g4[4];
         const float ciou = ciou_with_grad(pb, tb, g4);
         acc_box += (1.0f - ciou) * wgt;
-        acc_dfl += ce * 0.25f * wgt;                                                  // mean over 4 sides (:324) * weight
         const float kb = -(P.hyp_box * P.batch * inv_tss) * wgt;                      // L = (1-ciou)*w/tss
         // d/d(dist): x1 = gx - d0 -> -g4[0]; y1 -> -g4[1]; x2 = gx + d2 -> g4[2]; y2 -> g4[3]
         gd[0] = kb * -g4[0]; gd[1] = kb * -g4[1]; gd[2] = kb * g4[2]; gd[3] = kb * g4[3];
         cdfl = P.hyp_dfl * P.batch * inv_tss * 0.25f * wgt;
     }
-    if (WRITE_GRAD) {
+    // ---- one pass over the four sides: softmax statistics, DFL cross-entropy and all 16 gradients of a side
+    //      from the same 16 exponentials.
+    const float *xs = L.x[l] + img + i;
+    float *gs = WRITE_GRAD ? (L.g[l] + img + i) : nullptr;
+    float ce = 0.f;
 #pragma unroll 1
-        for (int s = 0; s < 4; ++s) {
-            // g_j = p_j * (gd*(j - d) + cdfl) - cdfl * ([j == tl] * wl + [j == tl+1] * wr)
-            const float gds = sel4(gd, s), m2s = sel4(m2, s), invs = sel4(inv_s, s), wls = sel4(wl, s);
-            const int tls = sel4(tl, s);
-            const float k0 = fmaf(-gds, sel4(dd, s), cdfl);
-            const float wr = 1.0f - wls;
-            float z[16];
-            if (fg) {
+    for (int s = 0; s < 4; ++s) {
+        float z[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) z[j] = __ldg(xin + (size_t)(s * 16 + j) * hw);
+        for (int j = 0; j < 16; ++j) z[j] = fg ? __ldg(xs + (size_t)j * hw) : 0.f;
+        float m = z[0];
+#pragma unroll
+        for (int j = 1; j < 16; ++j) m = fmaxf(m, z[j]);
+        const float mm = m * kLog2e;
+        float ssum = 0.f, dsum = 0.f;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            z[j] = ex2_fast(fmaf(z[j], kLog2e, -mm));
+            ssum += z[j];
+            dsum = fmaf(z[j], (float)j, dsum);
+        }
+        const float inv = rcp_fast(ssum);
+        const float d = dsum * inv;
+        const float t = fminf(fmaxf(sel4(tt, s), 0.f), 14.99f);                       // reg_max - 1 - 0.01 (:304)
+        const int tli = (int)t;
+        const float wls = (float)(tli + 1) - t, wrs = 1.0f - wls;
+        float zl = 0.f, zr = 0.f;
+        if (fg) {
+            zl = __ldg(xs + (size_t)tli * hw);
+            zr = __ldg(xs + (size_t)(tli + 1) * hw);
+        }
+        // cross-entropy at bins tl and tl+1 (:315-324): logsumexp = (mm + log2(sum)) * ln2
+        const float lse = (mm + __log2f(ssum)) * 0.69314718055994531f;
+        ce += (lse - zl) * wls + (lse - zr) * wrs;
+        if (WRITE_GRAD) {
+            // g_j = p_j * (gd*(j - d) + cdfl) - cdfl * ([j == tl] * wl + [j == tl+1] * wr),  p_j = e_j * inv
+            const float gds = sel4(gd, s);
+            const float ka = inv * gds, kb0 = inv * fmaf(-gds, d, cdfl);
+            if (live) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) gs[(size_t)j * hw] = z[j] * fmaf(ka, (float)j, kb0);
             }
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                float gval = 0.f;
-                if (fg) {
-                    const float pj = ex2_fast(fmaf(z[j], kLog2e, -m2s)) * invs;
-                    const float tj = (j == tls) ? wls : ((j == tls + 1) ? wr : 0.f);
-                    gval = fmaf(-cdfl, tj, pj * fmaf(gds, (float)j, k0));
-                }
-                if (live) gout[(size_t)(s * 16 + j) * hw] = gval;
+            if (fg) {      // the two target bins get their one-hot part (same thread, same address: ordered)
+                const float el = ex2_fast(fmaf(zl, kLog2e, -mm)), er = ex2_fast(fmaf(zr, kLog2e, -mm));
+                gs[(size_t)tli * hw] = fmaf(el, fmaf(ka, (float)tli, kb0), -cdfl * wls);
+                gs[(size_t)(tli + 1) * hw] = fmaf(er, fmaf(ka, (float)(tli + 1), kb0), -cdfl * wrs);
             }
         }
+        xs += (size_t)16 * hw;
+        if (WRITE_GRAD) gs += (size_t)16 * hw;
     }
+    acc_dfl += ce * 0.25f * wgt;                                                      // mean over 4 sides (:324) * weight
 }
 
 template <bool WRITE_GRAD>
@@ -294,14 +313,29 @@ __device__ __forceinline__ void loss_cls_item(const LevelSet &L, const LossParam
     // the class of anchor k relative to this item's first channel (never matches when background: lab = -1)
     const int r0 = lab4.x - c_lo, r1 = lab4.y - c_lo, r2 = lab4.z - c_lo, r3 = lab4.w - c_lo;
     const float gscale = P.hyp_cls * P.batch * inv_tss;
-    float acc = 0.f;
+    // targets pre-multiplied by the gradient scale: grad = sig*gscale - t*gscale, and sum(x*t) = sum(x*t*gscale)/gscale
+    // (hyp_cls == 0 makes the reported class loss 0 whatever this sum is)
+    const float inv_g = gscale != 0.f ? 1.0f / gscale : 0.f;
+    const float t0 = nr4.x * gscale, t1 = nr4.y * gscale, t2 = nr4.z * gscale, t3 = nr4.w * gscale;
+    // loss = sum max(x,0) - sum x*t + sum log1p(exp(-|x|)); the last sum is ONE log1p per lane of
+    // S = prod(1 + e) - 1, carried as S <- S + e + S*e (four independent chains, 16 factors each, S < 2^16).
+    float pos = 0.f, xt = 0.f;
+    float S0 = 0.f, S1 = 0.f, S2 = 0.f, S3 = 0.f;
+    auto elem = [&](float x, float tk, float &S) -> float {
+        const float e = ex2_fast(fabsf(x) * -kLog2e);      // exp(-|x|) in (0,1]
+        const float inv = rcp_fast(1.0f + e);               // sigmoid(|x|)
+        const float sg = x >= 0.f ? inv : e * inv;
+        S = fmaf(S, e, S + e);
+        pos += fmaxf(x, 0.f);
+        xt = fmaf(x, tk, xt);
+        return fmaf(sg, gscale, -tk);
+    };
     auto one = [&](const float4 xv, int c) -> float4 {
         float4 o;
-        float ls, sg, t;
-        t = (c == r0) ? nr4.x : 0.f; bce_logits(xv.x, t, ls, sg); acc += ls; o.x = (sg - t) * gscale;
-        t = (c == r1) ? nr4.y : 0.f; bce_logits(xv.y, t, ls, sg); acc += ls; o.y = (sg - t) * gscale;
-        t = (c == r2) ? nr4.z : 0.f; bce_logits(xv.z, t, ls, sg); acc += ls; o.z = (sg - t) * gscale;
-        t = (c == r3) ? nr4.w : 0.f; bce_logits(xv.w, t, ls, sg); acc += ls; o.w = (sg - t) * gscale;
+        o.x = elem(xv.x, c == r0 ? t0 : 0.f, S0);
+        o.y = elem(xv.y, c == r1 ? t1 : 0.f, S1);
+        o.z = elem(xv.z, c == r2 ? t2 : 0.f, S2);
+        o.w = elem(xv.w, c == r3 ? t3 : 0.f, S3);
         return o;
     };
     if (c_n == kClsGroup) {
@@ -323,7 +357,8 @@ __device__ __forceinline__ void loss_cls_item(const LevelSet &L, const LossParam
             if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)c * hw) = o;
         }
     }
-    acc_cls += acc;
+    const float S01 = fmaf(S0, S1, S0 + S1), S23 = fmaf(S2, S3, S2 + S3);
+    acc_cls += pos - xt * inv_g + log1pf(fmaf(S01, S23, S01 + S23));
 }
 
 template <bool WRITE_GRAD>
@@ -483,7 +518,7 @@ static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, i
     W.gt_label = c.take<int>(N);
     W.owned_cnt = c.take<int>(N);
     W.gt_flags = c.take<int>(N);
-    W.forced = c.take<int>(2 * N);
+    W.forced = c.take<int>(8 * N);
     W.gt_box = c.take<float4>(N);
     W.best_key = c.take<unsigned long long>(N);
     W.img_sum = c.take<double>((size_t)B);
@@ -560,7 +595,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
 
     if (stages & YS_STAGE_LOSS) {
         LossParams P;
-        P.tgi = io.tgi; P.lab = W.lab; P.norm = io.norm; P.gt_off = W.gt_off; P.gt_box = W.gt_box;
+        P.tgi = io.tgi; P.lab = W.lab; P.norm = io.norm; P.gt_off = W.gt_off; P.gt_box = W.gt_box; P.pbox = io.pbox;
         P.tss = W.tss; P.partials = W.partials; P.done = W.counters + 1; P.loss_out = loss_out;
         P.nc = nc; P.n_groups = (nc + kClsGroup - 1) / kClsGroup;
         P.items_per_img = L.n_segs + L.n_chunks * P.n_groups;
@@ -609,7 +644,7 @@ static void carve_assign(AssignWorkspace &W, void *base, size_t cap, int B, int 
     W.zero_bytes = align_up(c.off, 256);
     W.best_key = c.take<unsigned long long>(N);
     W.tss = c.take<float>(64);
-    W.forced = c.take<int>(2 * N);
+    W.forced = c.take<int>(8 * N);
     W.img_sum = c.take<double>((size_t)B);
     W.scan_partial = c.take<float>((size_t)B * scan_blocks(A));
     W.tgi = c.take<int>((size_t)B * A);
