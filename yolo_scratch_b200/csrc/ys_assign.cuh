@@ -18,7 +18,13 @@
 
 namespace ys {
 
-constexpr int kScanThreads = 256;
+#ifndef YS_SCAN_THREADS
+#define YS_SCAN_THREADS 256
+#endif
+#ifndef YS_SCAN_MINBLOCKS
+#define YS_SCAN_MINBLOCKS 4
+#endif
+constexpr int kScanThreads = YS_SCAN_THREADS;
 constexpr int kGtTile = 512;        // GT boxes staged per shared-memory tile
 constexpr int kFixSmemGt = 768;     // per-image GT count the fix-up handles with shared-memory scratch
 
@@ -38,7 +44,10 @@ struct AssignIO {
     // per-GT scratch, indexed like gt_box (zero on entry; re-zeroed by the fix-up)
     int *owned_cnt;
     int *gt_flags;              // 1: some anchor centre lies inside
-    unsigned long long *best_key;   // fix-up scratch when an image has more than kFixSmemGt GT
+    const unsigned char *risk;  // fused only (else nullptr): GT whose best-IoU anchor the scan computes (hint from k_pack_gt)
+    int skip_fixup;             // profiling only
+    unsigned long long *best_key;   // per-GT arg-max key over all anchors: written by the scan for risk GT (zero on
+                                    // entry), by the fix-up for the others when an image has more than kFixSmemGt GT
     int *forced;                // same: 8 ints per GT (forced x2, needy, kk, tg0, lost, spare x2)
     // per-anchor outputs (B,A)
     float4 *pbox;               // fused: decoded px boxes (written by the scan)
@@ -165,6 +174,8 @@ struct ScanSmem {
     float area[kGtTile];
     int any[kGtTile];
     int own[kGtTile];
+    unsigned long long rkey[kGtTile];   // arg-max keys of the tile's risk GT, indexed like rlist
+    unsigned short rlist[kGtTile];      // tile-relative indices of the risk GT
     unsigned char valid[kGtTile];
 };
 struct FixSmem {
@@ -185,10 +196,10 @@ template <bool FUSED>
 __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, FixSmem &S, int nblk);
 
 template <bool FUSED>
-__global__ void __launch_bounds__(kScanThreads, 4) k_assign(LevelSet L, AssignIO io, int B) {
+__global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS) k_assign(LevelSet L, AssignIO io, int B) {
     __shared__ AssignSmem sm;
     __shared__ float s_red[kScanThreads / 32];
-    __shared__ int s_flag;
+    __shared__ int s_flag, s_nrisk;
     ScanSmem &S = sm.s;
 
     const int b = blockIdx.y;
@@ -198,6 +209,7 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_assign(LevelSet L, AssignIO
 
     int g0, n;
     gt_range<FUSED>(io, b, g0, n);
+    if (tid == 0) s_nrisk = 0;     // images without GT never reach the staging code that resets it
 
     // ---- this anchor's predicted box (px) and centre (px)
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -249,6 +261,8 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_assign(LevelSet L, AssignIO
             const int tn = min(kGtTile, n - t0);
             if (pass == 0 || !one_tile) {
                 __syncthreads();
+                if (tid == 0) s_nrisk = 0;
+                __syncthreads();
                 for (int j = tid; j < tn; j += kScanThreads) {
                     const float4 q = io.gt_box[g0 + t0 + j];
                     S.box[j] = q;
@@ -256,6 +270,11 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_assign(LevelSet L, AssignIO
                     S.any[j] = 0;
                     S.own[j] = 0;
                     S.valid[j] = FUSED ? 1 : (io.gt_valid[g0 + t0 + j] != 0.f);
+                    if (FUSED && pass == 0 && io.risk[g0 + t0 + j]) {
+                        const int r = atomicAdd(&s_nrisk, 1);
+                        S.rlist[r] = (unsigned short)j;
+                        S.rkey[r] = 0ull;
+                    }
                 }
                 __syncthreads();
             }
@@ -269,10 +288,24 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_assign(LevelSet L, AssignIO
                         }
                     }
                 }
+                // risk GT: arg-max over all anchors of IoU(anchor, GT), first maximum (:136, :156) -- this block's
+                // share.  Warp: redux.max on the IoU bits (>= 0, so they order as integers), lowest lane among the ties.
+                const int nrisk = FUSED ? s_nrisk : 0;
+                if (nrisk > 0 && blockIdx.x * kScanThreads + (tid & ~31) < L.A) {     // warp-uniform
+                    for (int r = 0; r < nrisk; ++r) {
+                        const int j = S.rlist[r];
+                        const float ovr = live ? iou_assign_lazy(p, area_p, S.box[j], S.area[j]) : 0.f;
+                        const unsigned bits = __float_as_uint(ovr);
+                        const unsigned mx = __reduce_max_sync(0xffffffffu, bits);
+                        const unsigned who = __ballot_sync(0xffffffffu, bits == mx);
+                        if (lane == __ffs(who) - 1) atomicMax(&S.rkey[r], argmax_key(ovr, (unsigned)a));
+                    }
+                }
                 if (!one_tile) {
                     __syncthreads();
                     for (int j = tid; j < tn; j += kScanThreads)
                         if (S.any[j]) io.gt_flags[g0 + t0 + j] = 1;
+                    for (int r = tid; r < nrisk; r += kScanThreads) atomicMax(&io.best_key[g0 + t0 + S.rlist[r]], S.rkey[r]);
                 }
             } else if (cnt > 1) {
                 for (int j = 0; j < tn; ++j) {
@@ -316,6 +349,8 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_assign(LevelSet L, AssignIO
             if (S.own[j]) atomicAdd(&io.owned_cnt[g0 + j], S.own[j]);
             if (S.any[j]) io.gt_flags[g0 + j] = 1;
         }
+        if (FUSED)
+            for (int r = tid; r < s_nrisk; r += kScanThreads) atomicMax(&io.best_key[g0 + S.rlist[r]], S.rkey[r]);
     }
     if (tid == 0) {
         float tsum = 0.f;
@@ -334,6 +369,10 @@ __global__ void __launch_bounds__(kScanThreads, 4) k_assign(LevelSet L, AssignIO
     __syncthreads();
     if (!s_flag) return;
     __threadfence();
+    if (io.skip_fixup) {
+        if (tid == 0) io.img_done[b] = 0u;
+        return;
+    }
     fixup_image<FUSED>(L, io, b, B, sm.f, (int)gridDim.x);
 }
 
@@ -370,7 +409,7 @@ __device__ __forceinline__ void fix_argmax(const LevelSet &L, const AssignIO &io
 
 template <bool FUSED>
 __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, FixSmem &S, int nblk) {
-    __shared__ int s_nneedy, s_nlost, s_resume, s_nfired, s_want;
+    __shared__ int s_nneedy, s_ncmp, s_nlost, s_resume, s_nfired, s_want;
     __shared__ double s_delta[kScanThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kScanThreads / 32;
@@ -390,7 +429,7 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
     int *lost = in_smem ? S.lost : (gs + 5 * (size_t)n);
     unsigned long long *keyp = in_smem ? S.key : (io.best_key + g0);
 
-    if (tid == 0) { s_nneedy = 0; s_nlost = 0; }
+    if (tid == 0) { s_nneedy = 0; s_ncmp = 0; s_nlost = 0; }
     if (tid < kWarps) s_delta[tid] = 0.0;
     __syncthreads();
     // ---- A: which GT need a forced assignment?  (common case: none)
@@ -402,16 +441,22 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
         const bool lonely1 = valid && fl == 0;           // loop 1 (:117-139): valid GT with no anchor centre inside
         forced[2 * j] = lonely1 ? -2 : -1;               // -2: pending, resolved below
         forced[2 * j + 1] = -1;
-        keyp[j] = 0ull;
-        kk[j] = -1;
-        if (valid && (lonely1 || c == 0))                // loop 2 (:146-162) can only fire for GT that own nothing now
+        // risk GT: the scan already found the arg-max anchor (all blocks of the image are done: key is final)
+        const bool have = FUSED && io.risk != nullptr && io.risk[g0 + j];
+        const unsigned long long key = have ? __ldcg(io.best_key + g0 + j) : 0ull;
+        if (in_smem || !have) keyp[j] = key;
+        kk[j] = have ? (int)argmax_key_index(key) : -1;
+        if (valid && (lonely1 || c == 0)) {              // loop 2 (:146-162) can only fire for GT that own nothing now
             needy[atomicAdd(&s_nneedy, 1)] = j;
+            if (!have) lost[atomicAdd(&s_ncmp, 1)] = j;  // lost[] doubles as the "arg-max still to compute" list here
+        }
     }
     __syncthreads();
     const int nneedy = s_nneedy;
     if (nneedy > 0) {      // block-uniform
-        // ---- B: arg-max over all anchors of IoU(anchor, GT j), first maximum (:136, :156)
-        fix_argmax<FUSED>(L, io, b, g0, needy, nneedy, keyp);
+        // ---- B: arg-max over all anchors of IoU(anchor, GT j), first maximum (:136, :156), for the needy GT
+        //      the scan did not cover
+        if (s_ncmp > 0) fix_argmax<FUSED>(L, io, b, g0, lost, s_ncmp, keyp);
         __syncthreads();
         for (int q = tid; q < nneedy; q += kScanThreads) {
             const int j = needy[q];

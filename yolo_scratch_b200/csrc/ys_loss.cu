@@ -16,13 +16,33 @@ namespace ys {
 // =====================================================================================================
 constexpr int kPackThreads = 1024;
 constexpr int kPackSmemB = 8192;
+#ifndef YS_RISK_MAX_CENTRES
+#define YS_RISK_MAX_CENTRES 32
+#endif
+constexpr int kRiskMaxCentres = YS_RISK_MAX_CENTRES;   // GT with at most this many anchor centres inside get their best-IoU anchor from the scan
+
+// Number of grid centres c_i = (i + 0.5) * stride, i in [0, n), strictly inside (lo, hi) by the reference's test
+// (c - lo > 1e-9 and hi - c > 1e-9, losses/yolo_v8_loss.py:220-224).  Exact for short ranges; long ranges return
+// a lower bound > kRiskMaxCentres (the caller only asks "few or many").
+__device__ __forceinline__ int centres_inside(float lo, float hi, int n, float stride) {
+    int i0 = (int)floorf(lo / stride - 0.5f) - 1, i1 = (int)ceilf(hi / stride - 0.5f) + 1;
+    i0 = max(i0, 0);
+    i1 = min(i1, n - 1);
+    if (i1 - i0 > kRiskMaxCentres + 4) return i1 - i0 - 4;
+    int c = 0;
+    for (int i = i0; i <= i1; ++i) {
+        const float x = YS_MUL((float)i + 0.5f, stride);
+        c += (YS_SUB(x, lo) > kEpsInBox && YS_SUB(hi, x) > kEpsInBox) ? 1 : 0;
+    }
+    return c;
+}
 
 __global__ void __launch_bounds__(kPackThreads)
-k_pack_gt(const long long *__restrict__ batch_idx, const long long *__restrict__ cls, const float4 *__restrict__ bboxes,
+k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *__restrict__ cls, const float4 *__restrict__ bboxes,
           int N, int B, int nc, float sx, float sy, int *__restrict__ gt_off, int *__restrict__ rank,
           int *__restrict__ cursor_g, float4 *__restrict__ gt_box, int *__restrict__ gt_label,
-          unsigned long long *__restrict__ best_key, int *__restrict__ owned_cnt, int *__restrict__ gt_flags,
-          unsigned *__restrict__ counters, int n_counters) {
+          unsigned char *__restrict__ risk, unsigned long long *__restrict__ best_key, int *__restrict__ owned_cnt,
+          int *__restrict__ gt_flags, unsigned *__restrict__ counters, int n_counters) {
     __shared__ int s_cursor[kPackSmemB];
     __shared__ int s_part[kPackThreads / 32];
     __shared__ int s_unsorted;
@@ -131,7 +151,14 @@ k_pack_gt(const long long *__restrict__ batch_idx, const long long *__restrict__
         int dst = sorted ? i : (gt_off[(int)id] + rank[i]);
         float4 q = bboxes[i];
         // targets_bbox * [sx, sy, sx, sy]   (losses/yolo_v8_loss.py:515-516)
-        gt_box[dst] = make_float4(YS_MUL(q.x, sx), YS_MUL(q.y, sy), YS_MUL(q.z, sx), YS_MUL(q.w, sy));
+        const float4 qp = make_float4(YS_MUL(q.x, sx), YS_MUL(q.y, sy), YS_MUL(q.z, sx), YS_MUL(q.w, sy));
+        gt_box[dst] = qp;
+        // hint for k_assign: GT with few anchor centres inside are the ones the forced-assignment loops
+        // (:117-139, :146-162) can fire for; the scan computes their best-IoU anchor on the way.
+        int centres = 0;
+        for (int l = 0; l < L.n && centres <= kRiskMaxCentres; ++l)
+            centres += centres_inside(qp.x, qp.z, L.w[l], L.stride[l]) * centres_inside(qp.y, qp.w, L.hw[l] / L.w[l], L.stride[l]);
+        risk[dst] = centres <= kRiskMaxCentres ? 1 : 0;
         long long c = cls[i];
         c = c < 0 ? 0 : (c > nc - 1 ? nc - 1 : c);
         gt_label[dst] = (int)c;
@@ -493,6 +520,7 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
 
 struct LossWorkspace {
     int *gt_off, *rank, *cursor, *gt_label, *owned_cnt, *gt_flags, *forced, *tgi, *lab;
+    unsigned char *risk;
     float4 *gt_box, *pbox, *partials;
     unsigned long long *best_key;
     float *norm, *tss, *scan_partial;
@@ -518,6 +546,7 @@ static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, i
     W.gt_label = c.take<int>(N);
     W.owned_cnt = c.take<int>(N);
     W.gt_flags = c.take<int>(N);
+    W.risk = c.take<unsigned char>(N);
     W.forced = c.take<int>(8 * N);
     W.gt_box = c.take<float4>(N);
     W.best_key = c.take<unsigned long long>(N);
@@ -566,12 +595,12 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     if (target_gt_idx) { YS_REQUIRE(((uintptr_t)target_gt_idx & 15) == 0, YS_ERR_BAD_ARG, "target_gt_idx must be 16-byte aligned"); }
     if (norm_out) { YS_REQUIRE(((uintptr_t)norm_out & 15) == 0, YS_ERR_BAD_ARG, "norm must be 16-byte aligned"); }
 
-    if (stages == 0) stages = YS_STAGE_ALL;
+    if ((stages & YS_STAGE_ALL) == 0) stages |= YS_STAGE_ALL;
     if (stages & YS_STAGE_PACK) {
-        k_pack_gt<<<1, kPackThreads, 0, stream>>>((const long long *)batch_idx, (const long long *)cls,
+        k_pack_gt<<<1, kPackThreads, 0, stream>>>(L, (const long long *)batch_idx, (const long long *)cls,
                                                   (const float4 *)bboxes, n_gt, B, nc, scale_x, scale_y, W.gt_off, W.rank,
-                                                  W.cursor, W.gt_box, W.gt_label, W.best_key, W.owned_cnt, W.gt_flags,
-                                                  W.counters, B + 2);
+                                                  W.cursor, W.gt_box, W.gt_label, W.risk, W.best_key, W.owned_cnt,
+                                                  W.gt_flags, W.counters, B + 2);
         YS_CHECK_LAUNCH("k_pack_gt");
     }
 
@@ -579,6 +608,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     io.gt_off = W.gt_off; io.G = 0; io.gt_box = W.gt_box; io.gt_label_i = W.gt_label; io.gt_label_f = nullptr;
     io.gt_valid = nullptr; io.pd_box = nullptr; io.pd_scores = nullptr; io.anc = nullptr;
     io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags; io.forced = W.forced;
+    io.risk = W.risk; io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
     io.pbox = pred_boxes_px ? (float4 *)pred_boxes_px : W.pbox;
     io.tgi = target_gt_idx ? (int *)target_gt_idx : W.tgi;
     io.lab = W.lab;
@@ -687,6 +717,7 @@ extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, co
     io.gt_off = nullptr; io.G = G; io.gt_box = (const float4 *)gt_bboxes; io.gt_label_i = nullptr;
     io.gt_label_f = gt_labels; io.gt_valid = mask_gt; io.pd_box = (const float4 *)pd_bboxes; io.pd_scores = pd_scores;
     io.anc = (const float2 *)anc_points; io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags;
+    io.risk = nullptr; io.skip_fixup = 0;
     io.forced = W.forced; io.pbox = nullptr; io.tgi = W.tgi; io.lab = nullptr; io.norm = norm_out ? norm_out : W.norm;
     io.partial = W.scan_partial; io.img_sum = W.img_sum; io.tss = W.tss;
     io.done_counter = W.counters; io.img_done = W.counters + 2;
