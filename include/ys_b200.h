@@ -69,6 +69,7 @@ int ys_device_info(int *sm_count, int *cc_major, int *cc_minor);
 #define YS_STAGE_ASSIGN 2 /* k_assign   decode + scan + forced-assignment fix-up + target_scores_sum */
 #define YS_STAGE_LOSS 4   /* k_loss     BCE + CIoU + DFL forward and backward + ordered final reduction */
 #define YS_STAGE_ALL 7
+#define YS_STAGE_DIAG_LEGACY_LOSS 512 /* A/B only: run the non-persistent k_loss instead of k_loss_stream (same results) */
 #define YS_STAGE_DIAG_NOFIXUP 256 /* profiling only: k_assign skips the forced-assignment fix-up (results then differ) */
 size_t ys_detection_loss_workspace_bytes(int B, int A, int n_gt, int nc);
 int ys_detection_loss(int n_levels, const float *const *level_x_host, float *const *level_grad_host,

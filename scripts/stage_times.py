@@ -52,22 +52,22 @@ def main():
     wsb = torch.zeros(wbytes + 4096, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream(dev)
 
-    def call(stages=0):
-        rc = lib.ys_detection_loss(n, xp, gp, hs, ws_, st, B, nc, 16, bi.data_ptr(), cl.data_ptr(), bb.data_ptr(),
+    def call(stages=0, fwd_only=False):
+        rc = lib.ys_detection_loss(n, xp, None if fwd_only else gp, hs, ws_, st, B, nc, 16, bi.data_ptr(), cl.data_ptr(), bb.data_ptr(),
                                    n_gt, float(args.imgsz), float(args.imgsz), 7.5, 0.5, 1.5, 0.5, 4.0,
                                    out.data_ptr(), None, None, None, stages, wsb.data_ptr(), wsb.numel(),
                                    stream.cuda_stream)
         _lib.check(rc, "ys_detection_loss")
 
-    def timed(stages, reps):
+    def timed(stages, reps, fwd_only=False):
         call()
         for _ in range(3):
-            call(stages)
+            call(stages, fwd_only)
         torch.cuda.synchronize(dev)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(reps):
-            call(stages)
+            call(stages, fwd_only)
         e1.record(stream)
         torch.cuda.synchronize(dev)
         return e0.elapsed_time(e1) / reps * 1e3
@@ -83,6 +83,10 @@ def main():
     res["assign_nofix_us"] = timed(2 | 256, args.reps)
     call()
     res["loss_us"] = timed(4, args.reps)
+    res["loss_fwd_only_us"] = timed(4, args.reps, fwd_only=True)
+    res["loss_legacy_fwd_only_us"] = timed(4 | 512, args.reps, fwd_only=True)
+    call()
+    res["loss_legacy_us"] = timed(4 | 512, args.reps)
     res["full2_us"] = timed(0, args.reps)
     res["img_per_s"] = B / (res["full2_us"] * 1e-6)
     res["loss_items"] = out.tolist()

@@ -44,6 +44,7 @@ struct AssignIO {
     // per-GT scratch, indexed like gt_box (zero on entry; re-zeroed by the fix-up)
     int *owned_cnt;
     int *gt_flags;              // 1: some anchor centre lies inside
+    const int *img_order;       // fused only (else nullptr): blockIdx.y -> image, a scheduling hint from k_pack_gt
     const unsigned char *risk;  // fused only (else nullptr): GT whose best-IoU anchor the scan computes (hint from k_pack_gt)
     int skip_fixup;             // profiling only
     unsigned long long *best_key;   // per-GT arg-max key over all anchors: written by the scan for risk GT (zero on
@@ -63,6 +64,14 @@ struct AssignIO {
     int nc;
     float alpha, beta, eps;
 };
+
+__device__ __forceinline__ unsigned float_to_ord(float f) {
+    const unsigned u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord_to_float(unsigned o) {
+    return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o);
+}
 
 __device__ __forceinline__ int level_of(const LevelSet &L, int a) {
     int l = 0;
@@ -112,6 +121,20 @@ __device__ __forceinline__ float iou_assign_lazy(float4 p, float area_p, float4 
     const float uni = YS_ADD(YS_SUB(YS_ADD(area_p, area_q), inter), kEpsIou);
     const float iou = YS_DIV(inter, uni);
     return iou < 0.f ? 0.f : iou;
+}
+
+// Second "at risk" hint, evaluated where the image's GT are at hand (scan staging and fix-up must agree, so both call
+// this on the same boxes): GT j lies inside another GT's box -- every anchor centre inside j is then inside that GT
+// too, and j owns nothing if it loses all those arg-max contests (the loop-2 case, :146-162).  Small images only.
+constexpr int kContainMaxGt = 64;
+__device__ __forceinline__ bool gt_contained(const float4 *boxes, int n, int j) {
+    const float4 q = boxes[j];
+    bool c = false;
+    for (int k = 0; k < n; ++k) {
+        const float4 o = boxes[k];
+        c |= (k != j) && o.x <= q.x && o.y <= q.y && o.z >= q.z && o.w >= q.w;
+    }
+    return c;
 }
 
 // This anchor's centre (px) and, for the fused path, its grid position.
@@ -202,7 +225,7 @@ __global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS) k_assign(Leve
     __shared__ int s_flag, s_nrisk;
     ScanSmem &S = sm.s;
 
-    const int b = blockIdx.y;
+    const int b = (FUSED && io.img_order) ? io.img_order[blockIdx.y] : (int)blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int a = blockIdx.x * kScanThreads + tid;
     const bool live = a < L.A;
@@ -248,6 +271,12 @@ __global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS) k_assign(Leve
         }
     }
     const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
+    // bounding box of this warp's anchor centres (non-live lanes neutral); order-preserving float <-> uint map so
+    // that the dense entry point may be given any (also negative) anchor points
+    const float wx_min = ord_to_float(__reduce_min_sync(0xffffffffu, live ? float_to_ord(ax) : 0xffffffffu));
+    const float wx_max = ord_to_float(__reduce_max_sync(0xffffffffu, live ? float_to_ord(ax) : 0u));
+    const float wy_min = ord_to_float(__reduce_min_sync(0xffffffffu, live ? float_to_ord(ay) : 0xffffffffu));
+    const float wy_max = ord_to_float(__reduce_max_sync(0xffffffffu, live ? float_to_ord(ay) : 0u));
 
     int cnt = 0, first = -1, best_g = 0;
     float best_ov = -1.f;
@@ -277,11 +306,31 @@ __global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS) k_assign(Leve
                     }
                 }
                 __syncthreads();
+                if (FUSED && pass == 0 && n <= kContainMaxGt) {     // block-uniform; n <= 64 implies one tile
+                    if (tid < n && !io.risk[g0 + tid] && gt_contained(S.box, n, tid)) {
+                        const int r = atomicAdd(&s_nrisk, 1);
+                        S.rlist[r] = (unsigned short)tid;
+                        S.rkey[r] = 0ull;
+                    }
+                    __syncthreads();
+                }
             }
             if (pass == 0) {
-                if (live) {
-                    for (int j = 0; j < tn; ++j) {
-                        if (centre_in_box(ax, ay, S.box[j]) && S.valid[j]) {
+                // Warp-level prefilter: lane j asks whether GT j can contain ANY of the warp's anchor centres (their
+                // bounding box, by redux on the float bits -- centres are positive); the exact per-anchor test then
+                // runs over the few GT that pass, in ascending order.
+                for (int j0 = 0; j0 < tn; j0 += 32) {
+                    const int jl = j0 + lane;
+                    bool rel = false;
+                    if (jl < tn && S.valid[jl]) {
+                        const float4 q = S.box[jl];
+                        rel = q.x < wx_max && q.z > wx_min && q.y < wy_max && q.w > wy_min;
+                    }
+                    unsigned m = __ballot_sync(0xffffffffu, rel);
+                    while (m) {
+                        const int j = j0 + __ffs(m) - 1;
+                        m &= m - 1;
+                        if (live && centre_in_box(ax, ay, S.box[j])) {
                             if (first < 0) first = t0 + j;
                             ++cnt;
                             S.any[j] = 1;
@@ -391,19 +440,23 @@ __global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS) k_assign(Leve
 template <bool FUSED>
 __device__ __forceinline__ void fix_argmax(const LevelSet &L, const AssignIO &io, int b, int g0, const int *list,
                                            int nn, unsigned long long *keyp) {
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
     const float4 *pb = (FUSED ? io.pbox : io.pd_box) + (size_t)b * L.A;
-#pragma unroll 4
-    for (int a = tid; a < L.A; a += kScanThreads) {
-        const float4 p = FUSED ? __ldcg(pb + a) : pb[a];
-        const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
-        for (int q = 0; q < nn; ++q) {
-            const int j = list[q];
-            const float4 gq = io.gt_box[g0 + j];
-            const float ov = iou_assign_lazy(p, area_p, gq, area_eps_h(gq.x, gq.y, gq.z, gq.w));
-            const unsigned long long key = argmax_key(ov, (unsigned)a);
-            if (key > *((volatile unsigned long long *)&keyp[j])) atomicMax(&keyp[j], key);
+    for (int q = 0; q < nn; ++q) {
+        const int j = list[q];
+        const float4 gq = io.gt_box[g0 + j];
+        const float area_q = area_eps_h(gq.x, gq.y, gq.z, gq.w);
+        float best = -1.f;          // thread-local first maximum over this thread's anchors (ascending a)
+        int best_a = 0;
+#pragma unroll 8
+        for (int a = tid; a < L.A; a += kScanThreads) {
+            const float4 p = FUSED ? __ldcg(pb + a) : pb[a];
+            const float ov = iou_assign_lazy(p, area_eps_h(p.x, p.y, p.z, p.w), gq, area_q);
+            if (ov > best) { best = ov; best_a = a; }
         }
+        unsigned long long key = best >= 0.f ? argmax_key(best, (unsigned)best_a) : 0ull;
+        key = warp_max(key);
+        if (lane == 0) atomicMax(&keyp[j], key);
     }
 }
 
@@ -442,7 +495,8 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
         forced[2 * j] = lonely1 ? -2 : -1;               // -2: pending, resolved below
         forced[2 * j + 1] = -1;
         // risk GT: the scan already found the arg-max anchor (all blocks of the image are done: key is final)
-        const bool have = FUSED && io.risk != nullptr && io.risk[g0 + j];
+        const bool have = FUSED && io.risk != nullptr &&
+                          (io.risk[g0 + j] || (n <= kContainMaxGt && gt_contained(io.gt_box + g0, n, j)));
         const unsigned long long key = have ? __ldcg(io.best_key + g0 + j) : 0ull;
         if (in_smem || !have) keyp[j] = key;
         kk[j] = have ? (int)argmax_key_index(key) : -1;

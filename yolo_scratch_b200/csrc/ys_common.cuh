@@ -42,6 +42,8 @@ struct LevelSet {
     int chunk_off[YS_MAX_LEVELS + 1];   // first chunk of each level
     int seg_off[YS_MAX_LEVELS + 1];     // first 32-anchor segment of each level (box role of the loss kernel)
     int n_segs;                         // total 32-anchor segments per image
+    int hseg_off[YS_MAX_LEVELS + 1];    // first 16-anchor box item of each level (k_loss_stream)
+    int n_hsegs;                        // total 16-anchor box items per image
     float stride[YS_MAX_LEVELS];
 };
 

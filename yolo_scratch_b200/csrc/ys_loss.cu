@@ -7,7 +7,9 @@
 //               reference's forced-assignment loops; the last image computes target_scores_sum  [reads 64 box channels]
 //   k_loss      BCE + CIoU + DFL forward and backward, NCHW in, NCHW out; the last block reduces the partial
 //               sums in a fixed order                                                   [reads 144 ch, writes 144 ch]
+#include <string.h>
 #include "ys_assign.cuh"
+#include "ys_loss_stream.cuh"
 
 namespace ys {
 
@@ -19,22 +21,19 @@ constexpr int kPackSmemB = 8192;
 #ifndef YS_RISK_MAX_CENTRES
 #define YS_RISK_MAX_CENTRES 32
 #endif
-constexpr int kRiskMaxCentres = YS_RISK_MAX_CENTRES;   // GT with at most this many anchor centres inside get their best-IoU anchor from the scan
+constexpr int kRiskMaxCentres = YS_RISK_MAX_CENTRES;
+constexpr int kOrderMaxB = 1024;      // batches up to this size get their images ordered "fix-up likely" first   // GT with at most this many anchor centres inside get their best-IoU anchor from the scan
 
 // Number of grid centres c_i = (i + 0.5) * stride, i in [0, n), strictly inside (lo, hi) by the reference's test
-// (c - lo > 1e-9 and hi - c > 1e-9, losses/yolo_v8_loss.py:220-224).  Exact for short ranges; long ranges return
-// a lower bound > kRiskMaxCentres (the caller only asks "few or many").
+// (c - lo > 1e-9 and hi - c > 1e-9, losses/yolo_v8_loss.py:220-224).  Both predicates are monotonic in i, so the
+// first and last index are found by a short exact walk from an estimate.
 __device__ __forceinline__ int centres_inside(float lo, float hi, int n, float stride) {
     int i0 = (int)floorf(lo / stride - 0.5f) - 1, i1 = (int)ceilf(hi / stride - 0.5f) + 1;
-    i0 = max(i0, 0);
-    i1 = min(i1, n - 1);
-    if (i1 - i0 > kRiskMaxCentres + 4) return i1 - i0 - 4;
-    int c = 0;
-    for (int i = i0; i <= i1; ++i) {
-        const float x = YS_MUL((float)i + 0.5f, stride);
-        c += (YS_SUB(x, lo) > kEpsInBox && YS_SUB(hi, x) > kEpsInBox) ? 1 : 0;
-    }
-    return c;
+    i0 = min(max(i0, 0), n);
+    i1 = max(min(i1, n - 1), -1);
+    while (i0 < n && !(YS_SUB(YS_MUL((float)i0 + 0.5f, stride), lo) > kEpsInBox)) ++i0;
+    while (i1 >= 0 && !(YS_SUB(hi, YS_MUL((float)i1 + 0.5f, stride)) > kEpsInBox)) --i1;
+    return max(0, i1 - i0 + 1);
 }
 
 __global__ void __launch_bounds__(kPackThreads)
@@ -42,14 +41,16 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
           int N, int B, int nc, float sx, float sy, int *__restrict__ gt_off, int *__restrict__ rank,
           int *__restrict__ cursor_g, float4 *__restrict__ gt_box, int *__restrict__ gt_label,
           unsigned char *__restrict__ risk, unsigned long long *__restrict__ best_key, int *__restrict__ owned_cnt,
-          int *__restrict__ gt_flags, unsigned *__restrict__ counters, int n_counters) {
+          int *__restrict__ gt_flags, unsigned *__restrict__ counters, int n_counters, int *__restrict__ img_order) {
     __shared__ int s_cursor[kPackSmemB];
+    __shared__ int s_weight[kOrderMaxB];
     __shared__ int s_part[kPackThreads / 32];
     __shared__ int s_unsorted;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     volatile int *cursor = (B <= kPackSmemB) ? (volatile int *)s_cursor : (volatile int *)cursor_g;
     for (int i = tid; i < B; i += kPackThreads) cursor[i] = 0;
     for (int i = tid; i < n_counters; i += kPackThreads) counters[i] = 0u;    // arrival counters of k_assign / k_loss
+    for (int i = tid; i < kOrderMaxB; i += kPackThreads) s_weight[i] = 0;
     if (tid == 0) s_unsorted = 0;
     __syncthreads();
     // sorted and all ids valid?  (what the reference collate produces)
@@ -159,9 +160,26 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
         for (int l = 0; l < L.n && centres <= kRiskMaxCentres; ++l)
             centres += centres_inside(qp.x, qp.z, L.w[l], L.stride[l]) * centres_inside(qp.y, qp.w, L.hw[l] / L.w[l], L.stride[l]);
         risk[dst] = centres <= kRiskMaxCentres ? 1 : 0;
+        if (B <= kOrderMaxB && centres <= kRiskMaxCentres) atomicAdd(&s_weight[(int)id], centres <= 4 ? 64 : 1);
         long long c = cls[i];
         c = c < 0 ? 0 : (c > nc - 1 ? nc - 1 : c);
         gt_label[dst] = (int)c;
+    }
+    // Launch order of the images in k_assign (blockIdx.y -> image): the ones whose forced-assignment fix-up is
+    // likely to have work first, so that those fix-ups run under the scan of the remaining images instead of
+    // after it.  A scheduling hint only: results do not depend on the order.
+    __syncthreads();
+    for (int b = tid; b < B; b += kPackThreads) {
+        int r = b;
+        if (B <= kOrderMaxB) {
+            const int wb = s_weight[b];
+            r = 0;
+            for (int o = 0; o < B; ++o) {
+                const int wo = s_weight[o];
+                r += (wo > wb || (wo == wb && o < b)) ? 1 : 0;
+            }
+        }
+        img_order[r] = b;
     }
 }
 
@@ -366,16 +384,24 @@ __device__ __forceinline__ void loss_cls_item(const LevelSet &L, const LossParam
         return o;
     };
     if (c_n == kClsGroup) {
-#pragma unroll 1
-        for (int h = 0; h < kClsGroup; h += kClsBatch) {
-            float4 xv[kClsBatch];
+        // software pipeline: the loads of batch h+1 are in flight while batch h is computed and stored
+        float4 cur[kClsBatch], nxt[kClsBatch];
 #pragma unroll
-            for (int u = 0; u < kClsBatch; ++u) xv[u] = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)(h + u) * hw));
+        for (int u = 0; u < kClsBatch; ++u) cur[u] = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)u * hw));
+#pragma unroll
+        for (int h = 0; h < kClsGroup; h += kClsBatch) {
+            if (h + kClsBatch < kClsGroup) {
+#pragma unroll
+                for (int u = 0; u < kClsBatch; ++u)
+                    nxt[u] = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)(h + kClsBatch + u) * hw));
+            }
 #pragma unroll
             for (int u = 0; u < kClsBatch; ++u) {
-                const float4 o = one(xv[u], h + u);
+                const float4 o = one(cur[u], h + u);
                 if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)(h + u) * hw) = o;
             }
+#pragma unroll
+            for (int u = 0; u < kClsBatch; ++u) cur[u] = nxt[u];
         }
     } else {
         for (int c = 0; c < c_n; ++c) {
@@ -492,12 +518,14 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
     YS_REQUIRE(nc >= 1, YS_ERR_BAD_ARG, "nc must be >= 1");
     L.n = n_levels;
     L.C = 4 * reg_max + nc;
-    int a = 0, ch = 0, sg = 0;
+    int a = 0, ch = 0, sg = 0, hs16 = 0;
     for (int i = 0; i < n_levels; ++i) {
         YS_REQUIRE(xs[i] != nullptr && hs[i] > 0 && ws[i] > 0, YS_ERR_BAD_ARG, "level %d: null pointer or empty shape", i);
         YS_REQUIRE(((uintptr_t)xs[i] & 15) == 0, YS_ERR_BAD_ARG, "level %d: pointer must be 16-byte aligned", i);
         YS_REQUIRE((hs[i] * ws[i]) % 4 == 0, YS_ERR_UNSUPPORTED, "level %d: h*w must be a multiple of 4 (float4 path)", i);
         L.seg_off[i] = sg;
+        L.hseg_off[i] = hs16;
+        hs16 += (hs[i] * ws[i] + kBoxItem - 1) / kBoxItem;
         sg += (hs[i] * ws[i] + kSeg - 1) / kSeg;
         L.x[i] = xs[i];
         L.g[i] = gs ? gs[i] : nullptr;
@@ -510,16 +538,49 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
         a += L.hw[i];
         ch += (L.hw[i] + kChunk - 1) / kChunk;
     }
-    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.chunk_off[i] = ch; L.seg_off[i] = sg; }
+    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.chunk_off[i] = ch; L.seg_off[i] = sg; L.hseg_off[i] = hs16; }
     for (int i = n_levels; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; }
     L.A = a;
     L.n_chunks = ch;
     L.n_segs = sg;
+    L.n_hsegs = hs16;
+    return YS_OK;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static int build_stream_maps(StreamMaps &M, const LevelSet &L, int B) {
+    static EncodeTiledFn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t ce = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+        YS_REQUIRE(ce == cudaSuccess && fn != nullptr && q == cudaDriverEntryPointSuccess, YS_ERR_UNSUPPORTED,
+                   "cuTensorMapEncodeTiled is not available from this driver");
+        encode = (EncodeTiledFn)fn;
+    }
+    memset(&M, 0, sizeof(M));
+    for (int l = 0; l < L.n; ++l) {
+        const cuuint64_t gdim[2] = {(cuuint64_t)L.hw[l], (cuuint64_t)B * (cuuint64_t)L.C};
+        const cuuint64_t gstride[1] = {(cuuint64_t)L.hw[l] * 4u};
+        const cuuint32_t estr[2] = {1u, 1u};
+        const cuuint32_t box_b[2] = {(cuuint32_t)kBoxItem, 64u}, box_c[2] = {(cuuint32_t)kChunk, (cuuint32_t)kClsRows};
+        CUresult r = encode(&M.box[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)L.x[l], gdim, gstride, box_b, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        YS_REQUIRE(r == CUDA_SUCCESS, YS_ERR_BAD_ARG, "tensor map (box) of level %d: CUresult %d", l, (int)r);
+        r = encode(&M.cls[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)L.x[l], gdim, gstride, box_c, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        YS_REQUIRE(r == CUDA_SUCCESS, YS_ERR_BAD_ARG, "tensor map (cls) of level %d: CUresult %d", l, (int)r);
+    }
     return YS_OK;
 }
 
 struct LossWorkspace {
-    int *gt_off, *rank, *cursor, *gt_label, *owned_cnt, *gt_flags, *forced, *tgi, *lab;
+    int *gt_off, *rank, *cursor, *gt_label, *owned_cnt, *gt_flags, *forced, *tgi, *lab, *img_order;
     unsigned char *risk;
     float4 *gt_box, *pbox, *partials;
     unsigned long long *best_key;
@@ -542,6 +603,7 @@ static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, i
     W.tss = c.take<float>(64);
     W.gt_off = c.take<int>((size_t)B + 1);
     W.cursor = c.take<int>((size_t)B + 1);
+    W.img_order = c.take<int>((size_t)B);
     W.rank = c.take<int>(N);
     W.gt_label = c.take<int>(N);
     W.owned_cnt = c.take<int>(N);
@@ -556,7 +618,7 @@ static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, i
     W.lab = c.take<int>((size_t)B * A);
     W.norm = c.take<float>((size_t)B * A);
     W.pbox = c.take<float4>((size_t)B * A);
-    W.partials = c.take<float4>(loss_items_bound(B, A, nc) / kLossWarps + 2);
+    W.partials = c.take<float4>(loss_items_bound(B, A, nc) / kLossWarps + 2 + 4096);
     W.bytes = align_up(c.off, 256);
 }
 
@@ -600,7 +662,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         k_pack_gt<<<1, kPackThreads, 0, stream>>>(L, (const long long *)batch_idx, (const long long *)cls,
                                                   (const float4 *)bboxes, n_gt, B, nc, scale_x, scale_y, W.gt_off, W.rank,
                                                   W.cursor, W.gt_box, W.gt_label, W.risk, W.best_key, W.owned_cnt,
-                                                  W.gt_flags, W.counters, B + 2);
+                                                  W.gt_flags, W.counters, B + 2, W.img_order);
         YS_CHECK_LAUNCH("k_pack_gt");
     }
 
@@ -608,7 +670,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     io.gt_off = W.gt_off; io.G = 0; io.gt_box = W.gt_box; io.gt_label_i = W.gt_label; io.gt_label_f = nullptr;
     io.gt_valid = nullptr; io.pd_box = nullptr; io.pd_scores = nullptr; io.anc = nullptr;
     io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags; io.forced = W.forced;
-    io.risk = W.risk; io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
+    io.img_order = W.img_order; io.risk = W.risk; io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
     io.pbox = pred_boxes_px ? (float4 *)pred_boxes_px : W.pbox;
     io.tgi = target_gt_idx ? (int *)target_gt_idx : W.tgi;
     io.lab = W.lab;
@@ -623,7 +685,38 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         YS_CHECK_LAUNCH("k_assign");
     }
 
-    if (stages & YS_STAGE_LOSS) {
+    if ((stages & YS_STAGE_LOSS) && !(stages & YS_STAGE_DIAG_LEGACY_LOSS)) {
+        // persistent TMA-fed stream: one CTA per SM
+        StreamParams P;
+        P.tgi = io.tgi; P.lab = W.lab; P.norm = io.norm; P.gt_off = W.gt_off; P.gt_box = W.gt_box; P.pbox = io.pbox;
+        P.tss = W.tss; P.partials = W.partials; P.done = W.counters + 1; P.loss_out = loss_out;
+        P.nc = nc; P.n_groups = (nc + kClsRows - 1) / kClsRows;
+        P.n_box = L.n_hsegs;
+        P.items_per_img = L.n_hsegs + L.n_chunks * P.n_groups;
+        YS_REQUIRE((long long)B * P.items_per_img < 2147483647LL / 2, YS_ERR_UNSUPPORTED, "too many work items");
+        P.total_items = B * P.items_per_img;
+        P.hyp_box = hyp_box; P.hyp_cls = hyp_cls; P.hyp_dfl = hyp_dfl; P.batch = (float)B;
+        int dev = 0, sms = 0;
+        cudaError_t ce = cudaGetDevice(&dev);
+        if (ce == cudaSuccess) ce = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        YS_REQUIRE(ce == cudaSuccess && sms > 0, (int)(ce ? ce : cudaErrorUnknown), "cannot query the SM count: %s", cudaGetErrorString(ce));
+        const int want = (P.total_items + kStreamWarps - 1) / kStreamWarps;
+        const unsigned blocks = (unsigned)(want < sms ? (want > 0 ? want : 1) : (sms > 4096 ? 4096 : sms));
+        const size_t smem = (size_t)kStreamWarps * kStreamStages * kStageBytes;
+        StreamMaps M;
+        rc = build_stream_maps(M, L, B);
+        if (rc) return rc;
+        if (level_grad_host) {
+            ce = cudaFuncSetAttribute(k_loss_stream<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            YS_REQUIRE(ce == cudaSuccess, (int)ce, "k_loss_stream smem opt-in: %s", cudaGetErrorString(ce));
+            k_loss_stream<true><<<blocks, kStreamThreads, smem, stream>>>(L, P, M);
+        } else {
+            ce = cudaFuncSetAttribute(k_loss_stream<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            YS_REQUIRE(ce == cudaSuccess, (int)ce, "k_loss_stream smem opt-in: %s", cudaGetErrorString(ce));
+            k_loss_stream<false><<<blocks, kStreamThreads, smem, stream>>>(L, P, M);
+        }
+        YS_CHECK_LAUNCH("k_loss_stream");
+    } else if (stages & YS_STAGE_LOSS) {
         LossParams P;
         P.tgi = io.tgi; P.lab = W.lab; P.norm = io.norm; P.gt_off = W.gt_off; P.gt_box = W.gt_box; P.pbox = io.pbox;
         P.tss = W.tss; P.partials = W.partials; P.done = W.counters + 1; P.loss_out = loss_out;
@@ -710,14 +803,14 @@ extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, co
     LevelSet L;
     L.n = 1; L.A = A; L.C = nc; L.n_chunks = 0;
     for (int i = 0; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; }
-    for (int i = 0; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = i == 0 ? 0 : A; L.chunk_off[i] = 0; L.seg_off[i] = 0; }
-    L.n_segs = 0;
+    for (int i = 0; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = i == 0 ? 0 : A; L.chunk_off[i] = 0; L.seg_off[i] = 0; L.hseg_off[i] = 0; }
+    L.n_segs = 0; L.n_hsegs = 0;
 
     AssignIO io;
     io.gt_off = nullptr; io.G = G; io.gt_box = (const float4 *)gt_bboxes; io.gt_label_i = nullptr;
     io.gt_label_f = gt_labels; io.gt_valid = mask_gt; io.pd_box = (const float4 *)pd_bboxes; io.pd_scores = pd_scores;
     io.anc = (const float2 *)anc_points; io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags;
-    io.risk = nullptr; io.skip_fixup = 0;
+    io.img_order = nullptr; io.risk = nullptr; io.skip_fixup = 0;
     io.forced = W.forced; io.pbox = nullptr; io.tgi = W.tgi; io.lab = nullptr; io.norm = norm_out ? norm_out : W.norm;
     io.partial = W.scan_partial; io.img_sum = W.img_sum; io.tss = W.tss;
     io.done_counter = W.counters; io.img_done = W.counters + 2;

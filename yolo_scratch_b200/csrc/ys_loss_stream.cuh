@@ -1,0 +1,425 @@
+// ys_loss_stream.cuh -- k_loss_stream: the loss forward + backward kernel as a persistent, TMA-fed stream.
+//
+// Same arithmetic as k_loss (ys_loss.cu) -- BCE-with-logits, CIoU and DFL, forward and backward, replacing
+// losses/yolo_v8_loss.py:472-499 and :280-324 of the reference plus their autograd backward -- but the head values
+// are no longer loaded into registers by the warp that consumes them.  k_loss is latency bound (64 registers x
+// 32 warps per SM leave ~40 KB of loads in flight per SM); here every warp owns a two-stage ring of 4 KB
+// shared-memory tiles filled by bulk asynchronous copies (cp.async.bulk global -> shared, completion on an
+// mbarrier), so the tile of work item k+1 is in flight -- costing no registers -- while item k is computed:
+// 16 warps x 5 KB = 80 KB in flight per SM at all times.
+//
+//   grid      one CTA per SM (persistent), 16 warps; warp w of CTA c walks items c*16+w, +gridDim*16, ...
+//   items     image-major, per image first the box items, then the class items:
+//     box     16 anchors x 64 box channels (64 rows of 64 B).  Lane = (side pair, anchor): each half-warp runs two
+//             of the four sides, both halves evaluate the anchor's CIoU.  Items without a foreground anchor load
+//             nothing and only zero-fill their 4 KB of gradient.
+//     class   128 anchors x 8 class channels (8 rows of 512 B), float4 per lane per channel.
+//   aux       the per-anchor assignment the item needs (labels + target scores, or decoded boxes + target scores)
+//             rides in the same stage through the same mbarrier.
+//   output    gradients go straight from registers to HBM (full 32-byte sectors per store instruction).
+// Per-warp partial sums are carried across items and reduced once per CTA; the last CTA reduces the grid's
+// partials in a fixed order (fp64).  The item -> warp map is static, so results are run-to-run deterministic.
+#pragma once
+#include <cuda.h>
+#include "ys_common.cuh"
+
+namespace ys {
+
+constexpr int kStreamWarps = 16;
+constexpr int kStreamThreads = kStreamWarps * 32;
+constexpr int kStreamStages = 2;
+constexpr int kBoxItem = 16;             // anchors per box item
+constexpr int kClsRows = 8;              // class channels per class item
+constexpr int kTileFloats = 1024 + 16;   // 4 KB tile; the second side pair of a box tile sits 16 floats further (bank spread)
+constexpr int kAuxBytes = 1024;
+constexpr int kStageBytes = kTileFloats * 4 + kAuxBytes + 64;   // 5248, a multiple of 128
+static_assert(kStageBytes % 128 == 0, "stage size");
+
+struct StreamParams {
+    const int *tgi;          // (B,A) -1 = background
+    const int *lab;          // (B,A) class of the assigned GT, -1 = background
+    const float *norm;       // (B,A)
+    const int *gt_off;       // (B+1)
+    const float4 *gt_box;    // px
+    const float4 *pbox;      // (B,A) decoded boxes, px (written by k_assign)
+    const float *tss;        // [0]
+    float4 *partials;        // (gridDim.x)
+    unsigned *done;          // arrival counter, self-resetting
+    float *loss_out;         // [4]
+    int nc, n_groups;        // class channels, ceil(nc / kClsRows)
+    int n_box;               // box items per image
+    int items_per_img;       // n_box + n_chunks * n_groups
+    int total_items;         // B * items_per_img
+    float hyp_box, hyp_cls, hyp_dfl;
+    float batch;
+};
+
+// One 2-D tensor map per level and item kind over the level viewed as [B*C rows][h*w columns] fp32: a whole tile is
+// ONE TMA operation (row-by-row 1-D bulk copies of 64..512 B are TMA issue-rate bound: measured 2.8 TB/s).
+struct StreamMaps {
+    CUtensorMap box[YS_MAX_LEVELS];     // box {16 columns, 64 rows}
+    CUtensorMap cls[YS_MAX_LEVELS];     // box {128 columns, 8 rows}
+};
+
+// ---- mbarrier / bulk-copy primitives (PTX ISA: mbarrier, cp.async.bulk) ------------------------------------
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_g2s_2d(unsigned dst, const CUtensorMap *map, int col, int row, unsigned bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(col), "r"(row), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// ---- work item ------------------------------------------------------------------------------------------------
+struct Item {
+    int b, l, hw, i0;        // image, level, level size, first anchor within the level
+    int group;               // class items: channel group; box items: -1
+    int n_live;              // anchors of the item that exist (<= 16 or <= 128)
+};
+__device__ __forceinline__ Item decode_item(const LevelSet &L, const StreamParams &P, int item) {
+    Item it;
+    it.b = item / P.items_per_img;
+    const int r = item - it.b * P.items_per_img;
+    int l = 0;
+    if (r < P.n_box) {
+#pragma unroll
+        for (int k = 1; k < YS_MAX_LEVELS; ++k)
+            if (k < L.n && r >= L.hseg_off[k]) l = k;
+        it.i0 = (r - L.hseg_off[l]) * kBoxItem;
+        it.group = -1;
+        it.hw = L.hw[l];
+        it.n_live = min(kBoxItem, it.hw - it.i0);
+    } else {
+        const int q = r - P.n_box;
+#ifdef YS_CLS_CHUNK_MAJOR
+        const int chunk = q / P.n_groups;
+        it.group = q - chunk * P.n_groups;
+#else
+        // group-major: consecutive items (= the warps of one CTA) walk consecutive 512-byte pieces of the same rows
+        it.group = q / L.n_chunks;
+        const int chunk = q - it.group * L.n_chunks;
+#endif
+#pragma unroll
+        for (int k = 1; k < YS_MAX_LEVELS; ++k)
+            if (k < L.n && chunk >= L.chunk_off[k]) l = k;
+        it.i0 = (chunk - L.chunk_off[l]) * kChunk;
+        it.hw = L.hw[l];
+        it.n_live = min(kChunk, it.hw - it.i0);
+    }
+    it.l = l;
+    return it;
+}
+
+// Issue the bulk copies of one item into a stage (whole warp calls; lanes issue one or two rows each).
+// Returns nothing; the stage's mbarrier completes when all bytes have landed.  Box items: only when has_fg.
+__device__ __forceinline__ void issue_item(const LevelSet &L, const StreamParams &P, const StreamMaps &M, const Item &it,
+                                           char *stage, unsigned bar, int lane) {
+    const unsigned tile = smem_u32(stage), aux = tile + kTileFloats * 4;
+    const size_t arow = (size_t)it.b * L.A + L.a_off[it.l] + it.i0;
+    const unsigned rb = (unsigned)it.n_live * 4u;
+    // the tensor operation always delivers the full 4 KB box (columns past the level's end arrive as zeros)
+    if (it.group < 0) {
+        if (lane == 0) {
+            mbar_expect_tx(bar, 4096u + (unsigned)it.n_live * 20u);                   // tile + pbox (16 B) + norm (4 B)
+            tma_g2s_2d(tile, &M.box[it.l], it.i0, it.b * L.C, bar);
+            bulk_g2s(aux, P.pbox + arow, (unsigned)it.n_live * 16u, bar);
+            bulk_g2s(aux + 256u, P.norm + arow, rb, bar);
+        }
+    } else {
+        if (lane == 0) {
+            mbar_expect_tx(bar, 4096u + 2u * rb);
+            tma_g2s_2d(tile, &M.cls[it.l], it.i0, it.b * L.C + 64 + it.group * kClsRows, bar);
+            bulk_g2s(aux, P.lab + arow, rb, bar);
+            bulk_g2s(aux + 512u, P.norm + arow, rb, bar);
+        }
+    }
+}
+
+// ---- box item -------------------------------------------------------------------------------------------------
+template <bool WRITE_GRAD>
+__device__ __forceinline__ void stream_box_zero(const LevelSet &L, const Item &it, int lane) {
+    if (!WRITE_GRAD) return;
+    // 64 rows x 64 B: 4 lanes per row, 8 rows per instruction
+    float *g = L.g[it.l] + (size_t)it.b * L.C * it.hw + it.i0;
+    const int col = (lane & 3) * 4, rsub = lane >> 2;
+    if (col < it.n_live) {
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) *reinterpret_cast<float4 *>(g + (size_t)(c * 8 + rsub) * it.hw + col) = z4;
+    }
+}
+
+template <bool WRITE_GRAD>
+__device__ __forceinline__ void stream_box(const LevelSet &L, const StreamParams &P, const Item &it, const char *stage,
+                                           int tg, int lane, float inv_tss, float &acc_box, float &acc_dfl) {
+    const float *tile = reinterpret_cast<const float *>(stage);
+    const char *aux = stage + kTileFloats * 4;
+    const int sp = lane >> 4, a16 = lane & 15;
+    const int i = it.i0 + a16;
+    const bool live = a16 < it.n_live;
+    const bool fg = live && tg >= 0;
+    const float st = L.stride[it.l];
+    float gd0 = 0.f, gd1 = 0.f, tt0 = 0.f, tt1 = 0.f;     // this lane's two sides: CIoU gradient wrt the distance, DFL target
+    float cdfl = 0.f, wgt = 0.f;
+    if (fg) {
+        wgt = reinterpret_cast<const float *>(aux + 256)[a16];                        // target_scores.sum(-1) (:298)
+        const float4 q = __ldg(P.gt_box + __ldg(P.gt_off + it.b) + tg);
+        const float4 tb = make_float4(q.x / st, q.y / st, q.z / st, q.w / st);        // target_bboxes /= stride (:479)
+        const float4 pp = reinterpret_cast<const float4 *>(aux)[a16];                 // decoded by k_assign, pixels
+        const float4 pb = make_float4(pp.x / st, pp.y / st, pp.z / st, pp.w / st);    // back to grid units (:412)
+        const int w = L.w[it.l];
+        const int iy = i / w, ix = i - iy * w;
+        const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
+        float g4[4];
+        const float ciou = ciou_with_grad(pb, tb, g4);
+        if (sp == 0) acc_box += (1.0f - ciou) * wgt;                                  // one half-warp accounts the value
+        const float kb = -(P.hyp_box * P.batch * inv_tss) * wgt;                      // L = (1-ciou)*w/tss
+        // d/d(dist): x1 = gx - d0 -> -g4[0]; y1 -> -g4[1]; x2 = gx + d2 -> g4[2]; y2 -> g4[3]
+        // bbox2dist targets (:304, :327-330): l = gx - x1, t = gy - y1, r = x2 - gx, b = y2 - gy
+        if (sp == 0) { gd0 = kb * -g4[0]; gd1 = kb * -g4[1]; tt0 = gx - tb.x; tt1 = gy - tb.y; }
+        else         { gd0 = kb * g4[2];  gd1 = kb * g4[3];  tt0 = tb.z - gx; tt1 = tb.w - gy; }
+        cdfl = P.hyp_dfl * P.batch * inv_tss * 0.25f * wgt;
+    }
+    float *gs = WRITE_GRAD ? (L.g[it.l] + (size_t)it.b * L.C * it.hw + i) : nullptr;
+    float ce = 0.f;
+#pragma unroll 1
+    for (int s2 = 0; s2 < 2; ++s2) {
+        const int row0 = (sp * 2 + s2) * 16;                                          // first channel row of this side
+        const float *zs = tile + row0 * kBoxItem + a16;
+        float z[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) z[j] = fg ? zs[j * kBoxItem] : 0.f;
+        float m = z[0];
+#pragma unroll
+        for (int j = 1; j < 16; ++j) m = fmaxf(m, z[j]);
+        const float mm = m * kLog2e;
+        float ssum = 0.f, dsum = 0.f;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            z[j] = ex2_fast(fmaf(z[j], kLog2e, -mm));
+            ssum += z[j];
+            dsum = fmaf(z[j], (float)j, dsum);
+        }
+        const float inv = rcp_fast(ssum);
+        const float d = dsum * inv;
+        const float t = fminf(fmaxf(s2 ? tt1 : tt0, 0.f), 14.99f);                    // reg_max - 1 - 0.01 (:304)
+        const int tli = (int)t;
+        const float wls = (float)(tli + 1) - t, wrs = 1.0f - wls;
+        const float zl = fg ? zs[tli * kBoxItem] : 0.f, zr = fg ? zs[(tli + 1) * kBoxItem] : 0.f;
+        // cross-entropy at bins tl and tl+1 (:315-324): logsumexp = (mm + log2(sum)) * ln2
+        const float lse = (mm + __log2f(ssum)) * 0.69314718055994531f;
+        ce += (lse - zl) * wls + (lse - zr) * wrs;
+        if (WRITE_GRAD && live) {
+            // g_j = p_j * (gd*(j - d) + cdfl) - cdfl * ([j == tl] * wl + [j == tl+1] * wr),  p_j = e_j * inv
+            const float gds = s2 ? gd1 : gd0;
+            const float ka = inv * gds, kb0 = inv * fmaf(-gds, d, cdfl);
+            float *gr = gs + (size_t)row0 * it.hw;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) gr[(size_t)j * it.hw] = z[j] * fmaf(ka, (float)j, kb0);
+            if (fg) {      // the two target bins get their one-hot part (same thread, same address: ordered)
+                const float el = ex2_fast(fmaf(zl, kLog2e, -mm)), er = ex2_fast(fmaf(zr, kLog2e, -mm));
+                gr[(size_t)tli * it.hw] = fmaf(el, fmaf(ka, (float)tli, kb0), -cdfl * wls);
+                gr[(size_t)(tli + 1) * it.hw] = fmaf(er, fmaf(ka, (float)(tli + 1), kb0), -cdfl * wrs);
+            }
+        }
+    }
+    acc_dfl += ce * 0.25f * wgt;                                                      // mean over 4 sides (:324) * weight
+}
+
+// ---- class item -----------------------------------------------------------------------------------------------
+template <bool WRITE_GRAD>
+__device__ __forceinline__ void stream_cls(const LevelSet &L, const StreamParams &P, const Item &it, const char *stage,
+                                           int lane, float inv_tss, float &acc_cls) {
+    if (lane * 4 >= it.n_live) return;        // hw % 4 == 0 => the 4 anchors of a lane are live together
+    const float *tile = reinterpret_cast<const float *>(stage);
+    const char *aux = stage + kTileFloats * 4;
+    const int c_lo = it.group * kClsRows;
+    const int c_n = min(kClsRows, P.nc - c_lo);
+    const int4 lab4 = reinterpret_cast<const int4 *>(aux)[lane];
+    const float4 nr4 = reinterpret_cast<const float4 *>(aux + 512)[lane];
+    float *gc = WRITE_GRAD ? L.g[it.l] + ((size_t)it.b * L.C + 64 + c_lo) * it.hw + it.i0 + lane * 4 : nullptr;
+    // the class of anchor k relative to this item's first channel (never matches when background: lab = -1)
+    const int r0 = lab4.x - c_lo, r1 = lab4.y - c_lo, r2 = lab4.z - c_lo, r3 = lab4.w - c_lo;
+    const float gscale = P.hyp_cls * P.batch * inv_tss;
+    // targets pre-multiplied by the gradient scale: grad = sig*gscale - t*gscale, and sum(x*t) = sum(x*t*gscale)/gscale
+    const float inv_g = gscale != 0.f ? 1.0f / gscale : 0.f;
+    const float t0 = nr4.x * gscale, t1 = nr4.y * gscale, t2 = nr4.z * gscale, t3 = nr4.w * gscale;
+    // loss = sum max(x,0) - sum x*t + sum log1p(exp(-|x|)); the last sum is ONE log1p per lane of
+    // S = prod(1 + e) - 1, carried as S <- S + e + S*e (four independent chains, 8 factors each).
+    float pos = 0.f, xt = 0.f;
+    float S0 = 0.f, S1 = 0.f, S2 = 0.f, S3 = 0.f;
+    auto elem = [&](float x, float tk, float &S) -> float {
+        const float e = ex2_fast(fabsf(x) * -kLog2e);      // exp(-|x|) in (0,1]
+        const float inv = rcp_fast(1.0f + e);               // sigmoid(|x|)
+        const float sg = x >= 0.f ? inv : e * inv;
+        S = fmaf(S, e, S + e);
+        pos += fmaxf(x, 0.f);
+        xt = fmaf(x, tk, xt);
+        return fmaf(sg, gscale, -tk);
+    };
+    auto one = [&](const float4 xv, int c) -> float4 {
+        float4 o;
+        o.x = elem(xv.x, c == r0 ? t0 : 0.f, S0);
+        o.y = elem(xv.y, c == r1 ? t1 : 0.f, S1);
+        o.z = elem(xv.z, c == r2 ? t2 : 0.f, S2);
+        o.w = elem(xv.w, c == r3 ? t3 : 0.f, S3);
+        return o;
+    };
+    if (c_n == kClsRows) {
+#pragma unroll
+        for (int c = 0; c < kClsRows; ++c) {
+            const float4 o = one(*reinterpret_cast<const float4 *>(tile + c * kChunk + lane * 4), c);
+            if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)c * it.hw) = o;
+        }
+    } else {
+        for (int c = 0; c < c_n; ++c) {
+            const float4 o = one(*reinterpret_cast<const float4 *>(tile + c * kChunk + lane * 4), c);
+            if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)c * it.hw) = o;
+        }
+    }
+    const float S01 = fmaf(S0, S1, S0 + S1), S23 = fmaf(S2, S3, S2 + S3);
+    acc_cls += pos - xt * inv_g + log1pf(fmaf(S01, S23, S01 + S23));
+}
+
+// ---- kernel ---------------------------------------------------------------------------------------------------
+template <bool WRITE_GRAD>
+__global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, StreamParams P, const __grid_constant__ StreamMaps M) {
+    extern __shared__ __align__(128) char s_ring[];                 // [warp][stage][kStageBytes]
+    __shared__ __align__(8) unsigned long long s_bar[kStreamWarps][kStreamStages];
+    __shared__ float s_sum[kStreamWarps][3];
+    __shared__ double s_fin[kStreamWarps][3];
+    __shared__ int s_last;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < kStreamStages; ++s) mbar_init(smem_u32(&s_bar[warp][s]), 1u);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+
+    const float inv_tss = 1.0f / P.tss[0];
+    float acc_box = 0.f, acc_cls = 0.f, acc_dfl = 0.f;
+    char *ring = s_ring + (size_t)warp * kStreamStages * kStageBytes;
+    const int step = (int)gridDim.x * kStreamWarps;
+    int item = (int)blockIdx.x * kStreamWarps + warp;
+
+    // Foreground lookup of a box item: every lane reads the assignment of "its" anchor (both half-warps the same 16).
+    auto load_tg = [&](const Item &it) -> int {
+        if (it.group >= 0) return -1;
+#ifdef YS_EXP_NOBOX
+        return -1;
+#endif
+        const int a16 = lane & 15;
+        return a16 < it.n_live ? __ldg(P.tgi + (size_t)it.b * L.A + L.a_off[it.l] + it.i0 + a16) : -1;
+    };
+    // Pipeline state: cur = item being computed, nxt = item whose tile is in flight, nn = item whose tgi is in flight.
+    Item cur, nxt, nn;
+    int tg_cur = -1, tg_nxt = -1, tg_nn = -1;
+    bool cur_loaded = false, nxt_loaded = false;
+    unsigned phase_bits = 0u;                                        // bit s = parity the next wait on stage s uses
+    const bool have0 = item < P.total_items, have1 = item + step < P.total_items, have2 = item + 2 * step < P.total_items;
+    if (have0) {
+        cur = decode_item(L, P, item);
+        tg_cur = load_tg(cur);
+        cur_loaded = cur.group >= 0 || __any_sync(0xffffffffu, tg_cur >= 0);
+        if (cur_loaded) issue_item(L, P, M, cur, ring, smem_u32(&s_bar[warp][0]), lane);
+    }
+    if (have1) {
+        nxt = decode_item(L, P, item + step);
+        tg_nxt = load_tg(nxt);
+    }
+    (void)have2;
+    int k = 0;
+    for (; item < P.total_items; item += step, ++k) {
+        const int s = k & 1;
+        // ---- launch the next item's tile into the other stage (its previous reader finished last iteration)
+        const bool has_nxt = item + step < P.total_items;
+        if (has_nxt) {
+            nxt_loaded = nxt.group >= 0 || __any_sync(0xffffffffu, tg_nxt >= 0);
+            __syncwarp();
+            fence_async_smem();
+            if (nxt_loaded) issue_item(L, P, M, nxt, ring + (size_t)(s ^ 1) * kStageBytes, smem_u32(&s_bar[warp][s ^ 1]), lane);
+            // and the assignment lookup of the one after it
+            if (item + 2 * step < P.total_items) {
+                nn = decode_item(L, P, item + 2 * step);
+                tg_nn = load_tg(nn);
+            }
+        }
+        // ---- compute the current item
+        const char *stage = ring + (size_t)s * kStageBytes;
+        if (cur_loaded) {
+            mbar_wait(smem_u32(&s_bar[warp][s]), (phase_bits >> s) & 1u);
+            phase_bits ^= 1u << s;
+            if (cur.group >= 0) stream_cls<WRITE_GRAD>(L, P, cur, stage, lane, inv_tss, acc_cls);
+            else stream_box<WRITE_GRAD>(L, P, cur, stage, tg_cur, lane, inv_tss, acc_box, acc_dfl);
+        } else {
+            stream_box_zero<WRITE_GRAD>(L, cur, lane);
+        }
+        cur = nxt; tg_cur = tg_nxt; cur_loaded = nxt_loaded;
+        nxt = nn; tg_nxt = tg_nn;
+    }
+
+    // ------------------------------------------------------------------ CTA partial sums (fixed order)
+    acc_box = warp_sum(acc_box);
+    acc_cls = warp_sum(acc_cls);
+    acc_dfl = warp_sum(acc_dfl);
+    if (lane == 0) { s_sum[warp][0] = acc_box; s_sum[warp][1] = acc_cls; s_sum[warp][2] = acc_dfl; }
+    __syncthreads();
+    if (tid == 0) {
+        float t0 = 0.f, t1 = 0.f, t2 = 0.f;
+#pragma unroll
+        for (int w = 0; w < kStreamWarps; ++w) { t0 += s_sum[w][0]; t1 += s_sum[w][1]; t2 += s_sum[w][2]; }
+        P.partials[blockIdx.x] = make_float4(t0, t1, t2, 0.f);
+        __threadfence();
+        const unsigned prev = atomicAdd(P.done, 1u);
+        s_last = (prev == gridDim.x - 1u);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    // ------------------------------------------------------------------ last CTA: ordered fp64 reduction
+    __threadfence();
+    double a0 = 0, a1 = 0, a2 = 0;
+    for (int i = tid; i < (int)gridDim.x; i += kStreamThreads) {
+        const float4 v = __ldcg(P.partials + i);
+        a0 += v.x; a1 += v.y; a2 += v.z;
+    }
+    a0 = warp_sum(a0); a1 = warp_sum(a1); a2 = warp_sum(a2);
+    if (lane == 0) { s_fin[warp][0] = a0; s_fin[warp][1] = a1; s_fin[warp][2] = a2; }
+    __syncthreads();
+    if (tid == 0) {
+        double t0 = 0, t1 = 0, t2 = 0;
+        for (int w = 0; w < kStreamWarps; ++w) { t0 += s_fin[w][0]; t1 += s_fin[w][1]; t2 += s_fin[w][2]; }
+        const double inv = 1.0 / (double)P.tss[0];
+        // loss[0] = box/tss*hyp_box, loss[1] = cls/tss*hyp_cls, loss[2] = dfl/tss*hyp_dfl (:475, :300, :306, :495-497)
+        const float lb = (float)(t0 * inv) * P.hyp_box;
+        const float lc = (float)(t1 * inv) * P.hyp_cls;
+        const float ld = (float)(t2 * inv) * P.hyp_dfl;
+        P.loss_out[0] = (lb + lc + ld) * P.batch;   // loss.sum() * batch_size (:499)
+        P.loss_out[1] = lb;
+        P.loss_out[2] = lc;
+        P.loss_out[3] = ld;
+        *P.done = 0u;
+    }
+}
+
+}  // namespace ys
