@@ -14,6 +14,7 @@
 //                "best-IoU anchor" (arg-max over all anchors) is computed here, lazily, only for the GT that
 //                need it.  Then the image's sum of target scores; the last image computes target_scores_sum.
 #pragma once
+#include <cuda.h>
 #include "ys_common.cuh"
 
 namespace ys {
@@ -25,8 +26,14 @@ namespace ys {
 #define YS_SCAN_MINBLOCKS 4
 #endif
 constexpr int kScanThreads = YS_SCAN_THREADS;
-constexpr int kGtTile = 512;        // GT boxes staged per shared-memory tile
-constexpr int kFixSmemGt = 768;     // per-image GT count the fix-up handles with shared-memory scratch
+constexpr int kGtTile = 256;        // GT boxes staged per shared-memory tile
+constexpr int kFixSmemGt = 256;     // per-image GT count the fix-up handles with shared-memory scratch
+constexpr int kScanTileBytes = 64 * kScanThreads * 4;   // fused path: 64 box channels x 256 anchors, one TMA operation
+
+// Fused path: one 2-D tensor map per level over [B*C rows][h*w columns] fp32, box {kScanThreads columns, 64 rows}.
+struct ScanMaps {
+    CUtensorMap lvl[YS_MAX_LEVELS];
+};
 
 // Everything the assignment kernel needs to know about where boxes, scores and GT come from.
 struct AssignIO {
@@ -123,20 +130,6 @@ __device__ __forceinline__ float iou_assign_lazy(float4 p, float area_p, float4 
     return iou < 0.f ? 0.f : iou;
 }
 
-// Second "at risk" hint, evaluated where the image's GT are at hand (scan staging and fix-up must agree, so both call
-// this on the same boxes): GT j lies inside another GT's box -- every anchor centre inside j is then inside that GT
-// too, and j owns nothing if it loses all those arg-max contests (the loop-2 case, :146-162).  Small images only.
-constexpr int kContainMaxGt = 64;
-__device__ __forceinline__ bool gt_contained(const float4 *boxes, int n, int j) {
-    const float4 q = boxes[j];
-    bool c = false;
-    for (int k = 0; k < n; ++k) {
-        const float4 o = boxes[k];
-        c |= (k != j) && o.x <= q.x && o.y <= q.y && o.z >= q.z && o.w >= q.w;
-    }
-    return c;
-}
-
 // This anchor's centre (px) and, for the fused path, its grid position.
 template <bool FUSED>
 __device__ __forceinline__ void anchor_centre(const AssignIO &io, const LevelSet &L, int a, float &ax, float &ay) {
@@ -219,39 +212,91 @@ template <bool FUSED>
 __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, FixSmem &S, int nblk);
 
 template <bool FUSED>
-__global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS) k_assign(LevelSet L, AssignIO io, int B) {
-    __shared__ AssignSmem sm;
+__global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS)
+k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
+    // dynamic shared memory: [fused: 64 x 256 fp32 tile of the block's box channels][AssignSmem]
+    extern __shared__ __align__(128) unsigned char s_dyn[];
+    AssignSmem &sm = *reinterpret_cast<AssignSmem *>(s_dyn + (FUSED ? kScanTileBytes : 0));
+    __shared__ __align__(8) unsigned long long s_mbar;
     __shared__ float s_red[kScanThreads / 32];
     __shared__ int s_flag, s_nrisk;
     ScanSmem &S = sm.s;
 
     const int b = (FUSED && io.img_order) ? io.img_order[blockIdx.y] : (int)blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int a = blockIdx.x * kScanThreads + tid;
-    const bool live = a < L.A;
+    // fused: blocks are cut per level (a block never straddles two levels: one tensor operation loads its tile)
+    int lvl = 0, i_lvl = 0, a;
+    bool live;
+    if (FUSED) {
+#pragma unroll
+        for (int k = 1; k < YS_MAX_LEVELS; ++k)
+            if (k < L.n && (int)blockIdx.x >= L.sblk_off[k]) lvl = k;
+        const int i0 = ((int)blockIdx.x - L.sblk_off[lvl]) * kScanThreads;
+        i_lvl = i0 + tid;
+        live = i_lvl < L.hw[lvl];
+        a = L.a_off[lvl] + i_lvl;
+        if (tid == 0) {
+            const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_mbar);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kScanTileBytes) : "memory");
+            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                         ::"r"((unsigned)__cvta_generic_to_shared(s_dyn)), "l"(&M.lvl[lvl]), "r"(i0), "r"(b * L.C), "r"(bar) : "memory");
+        }
+    } else {
+        a = blockIdx.x * kScanThreads + tid;
+        live = a < L.A;
+    }
 
     int g0, n;
     gt_range<FUSED>(io, b, g0, n);
-    if (tid == 0) s_nrisk = 0;     // images without GT never reach the staging code that resets it
+    const int ntiles = (n + kGtTile - 1) / kGtTile;
+    const bool one_tile = ntiles <= 1;
+    if (tid == 0) s_nrisk = 0;
+    // GT tile -> shared memory (no barriers inside; the caller brackets it)
+    auto stage_gt = [&](int t0, int tn, bool register_risk) {
+        for (int j = tid; j < tn; j += kScanThreads) {
+            const float4 q = io.gt_box[g0 + t0 + j];
+            S.box[j] = q;
+            S.area[j] = area_eps_h(q.x, q.y, q.z, q.w);
+            S.any[j] = 0;
+            S.own[j] = 0;
+            S.valid[j] = FUSED ? 1 : (io.gt_valid[g0 + t0 + j] != 0.f);
+            if (FUSED && register_risk && io.risk[g0 + t0 + j]) {
+                const int r = atomicAdd(&s_nrisk, 1);
+                S.rlist[r] = (unsigned short)j;
+                S.rkey[r] = 0ull;
+            }
+        }
+    };
+    __syncthreads();               // s_nrisk reset and (fused) mbarrier initialised
+    if (ntiles > 0) stage_gt(0, min(kGtTile, n), true);      // overlaps the tile load of the fused path
+    __syncthreads();
 
     // ---- this anchor's predicted box (px) and centre (px)
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
     float ax = 0.f, ay = 0.f;
-    if (live) {
-        if (FUSED) {
-            const int l = level_of(L, a);
-            const int i = a - L.a_off[l];
-            const int w = L.w[l], hw = L.hw[l];
-            const float st = L.stride[l];
-            const int iy = i / w, ix = i - iy * w;
+    if (FUSED) {
+        {
+            const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_mbar);
+            unsigned ok;
+            do {
+                asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}\n"
+                             : "=r"(ok) : "r"(bar) : "memory");
+            } while (!ok);
+        }
+        if (live) {
+            const int w = L.w[lvl];
+            const float st = L.stride[lvl];
+            const int iy = i_lvl / w, ix = i_lvl - iy * w;
             const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
-            const float *base = L.x[l] + (size_t)b * L.C * hw + i;
+            const float *col = reinterpret_cast<const float *>(s_dyn) + tid;
             float d[4];
 #pragma unroll
             for (int s = 0; s < 4; ++s) {
                 float z[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) z[j] = __ldg(base + (size_t)(s * 16 + j) * hw);
+                for (int j = 0; j < 16; ++j) z[j] = col[(s * 16 + j) * kScanThreads];
                 float m2, inv_s;
                 d[s] = dfl_stats16(z, m2, inv_s);
             }
@@ -263,12 +308,12 @@ __global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS) k_assign(Leve
             ax = YS_MUL(gx, st);
             ay = YS_MUL(gy, st);
             io.pbox[(size_t)b * L.A + a] = p;
-        } else {
-            p = io.pd_box[(size_t)b * L.A + a];
-            const float2 c = io.anc[a];
-            ax = c.x;
-            ay = c.y;
         }
+    } else if (live) {
+        p = io.pd_box[(size_t)b * L.A + a];
+        const float2 c = io.anc[a];
+        ax = c.x;
+        ay = c.y;
     }
     const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
     // bounding box of this warp's anchor centres (non-live lanes neutral); order-preserving float <-> uint map so
@@ -280,40 +325,18 @@ __global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS) k_assign(Leve
 
     int cnt = 0, first = -1, best_g = 0;
     float best_ov = -1.f;
-    const int ntiles = (n + kGtTile - 1) / kGtTile;
-    const bool one_tile = ntiles <= 1;
 
     // ---- pass 0: centre-in-box per GT (losses/yolo_v8_loss.py:210-224); pass 1: IoU arg-max for multi-hit anchors
     for (int pass = 0; pass < 2; ++pass) {
         for (int t = 0; t < ntiles; ++t) {
             const int t0 = t * kGtTile;
             const int tn = min(kGtTile, n - t0);
-            if (pass == 0 || !one_tile) {
+            if ((pass == 0 && t > 0) || (pass == 1 && !one_tile)) {       // tile 0 of pass 0 was staged above
                 __syncthreads();
                 if (tid == 0) s_nrisk = 0;
                 __syncthreads();
-                for (int j = tid; j < tn; j += kScanThreads) {
-                    const float4 q = io.gt_box[g0 + t0 + j];
-                    S.box[j] = q;
-                    S.area[j] = area_eps_h(q.x, q.y, q.z, q.w);
-                    S.any[j] = 0;
-                    S.own[j] = 0;
-                    S.valid[j] = FUSED ? 1 : (io.gt_valid[g0 + t0 + j] != 0.f);
-                    if (FUSED && pass == 0 && io.risk[g0 + t0 + j]) {
-                        const int r = atomicAdd(&s_nrisk, 1);
-                        S.rlist[r] = (unsigned short)j;
-                        S.rkey[r] = 0ull;
-                    }
-                }
+                stage_gt(t0, tn, pass == 0);
                 __syncthreads();
-                if (FUSED && pass == 0 && n <= kContainMaxGt) {     // block-uniform; n <= 64 implies one tile
-                    if (tid < n && !io.risk[g0 + tid] && gt_contained(S.box, n, tid)) {
-                        const int r = atomicAdd(&s_nrisk, 1);
-                        S.rlist[r] = (unsigned short)tid;
-                        S.rkey[r] = 0ull;
-                    }
-                    __syncthreads();
-                }
             }
             if (pass == 0) {
                 // Warp-level prefilter: lane j asks whether GT j can contain ANY of the warp's anchor centres (their
@@ -340,7 +363,7 @@ __global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS) k_assign(Leve
                 // risk GT: arg-max over all anchors of IoU(anchor, GT), first maximum (:136, :156) -- this block's
                 // share.  Warp: redux.max on the IoU bits (>= 0, so they order as integers), lowest lane among the ties.
                 const int nrisk = FUSED ? s_nrisk : 0;
-                if (nrisk > 0 && blockIdx.x * kScanThreads + (tid & ~31) < L.A) {     // warp-uniform
+                if (nrisk > 0 && __any_sync(0xffffffffu, live)) {     // warp-uniform
                     for (int r = 0; r < nrisk; ++r) {
                         const int j = S.rlist[r];
                         const float ovr = live ? iou_assign_lazy(p, area_p, S.box[j], S.area[j]) : 0.f;
@@ -363,7 +386,12 @@ __global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS) k_assign(Leve
                 }
             }
         }
-        if (pass == 0 && !__syncthreads_or(cnt > 1)) break;
+        // pass 1 only where some anchor sits in more than one GT: per warp when the GT are already staged,
+        // per block when pass 1 has to re-stage tiles
+        if (pass == 0) {
+            if (one_tile) { if (!__any_sync(0xffffffffu, cnt > 1)) break; }
+            else if (!__syncthreads_or(cnt > 1)) break;
+        }
     }
 
     // ---- preliminary per-anchor resolve (no forced entries yet): losses/yolo_v8_loss.py:226-244
@@ -495,8 +523,7 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
         forced[2 * j] = lonely1 ? -2 : -1;               // -2: pending, resolved below
         forced[2 * j + 1] = -1;
         // risk GT: the scan already found the arg-max anchor (all blocks of the image are done: key is final)
-        const bool have = FUSED && io.risk != nullptr &&
-                          (io.risk[g0 + j] || (n <= kContainMaxGt && gt_contained(io.gt_box + g0, n, j)));
+        const bool have = FUSED && io.risk != nullptr && io.risk[g0 + j];
         const unsigned long long key = have ? __ldcg(io.best_key + g0 + j) : 0ull;
         if (in_smem || !have) keyp[j] = key;
         kk[j] = have ? (int)argmax_key_index(key) : -1;

@@ -44,6 +44,8 @@ struct LevelSet {
     int n_segs;                         // total 32-anchor segments per image
     int hseg_off[YS_MAX_LEVELS + 1];    // first 16-anchor box item of each level (k_loss_stream)
     int n_hsegs;                        // total 16-anchor box items per image
+    int sblk_off[YS_MAX_LEVELS + 1];    // first 256-anchor scan block of each level (k_assign, fused path)
+    int n_sblk;                         // scan blocks per image
     float stride[YS_MAX_LEVELS];
 };
 

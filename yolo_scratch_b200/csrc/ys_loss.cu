@@ -22,6 +22,7 @@ constexpr int kPackSmemB = 8192;
 #define YS_RISK_MAX_CENTRES 32
 #endif
 constexpr int kRiskMaxCentres = YS_RISK_MAX_CENTRES;
+constexpr int kContainMaxGt = 64;     // images with at most this many GT get the containment hint
 constexpr int kOrderMaxB = 1024;      // batches up to this size get their images ordered "fix-up likely" first   // GT with at most this many anchor centres inside get their best-IoU anchor from the scan
 
 // Number of grid centres c_i = (i + 0.5) * stride, i in [0, n), strictly inside (lo, hi) by the reference's test
@@ -164,6 +165,26 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
         long long c = cls[i];
         c = c < 0 ? 0 : (c > nc - 1 ? nc - 1 : c);
         gt_label[dst] = (int)c;
+    }
+    // Second "at risk" hint (small images only): GT j lies inside another GT's box -- every anchor centre inside j is
+    // then inside that GT too, and j owns nothing if it loses all those arg-max contests (the loop-2 case, :146-162).
+    __syncthreads();
+    for (int i = tid; i < N; i += kPackThreads) {
+        const long long id = batch_idx[i];
+        if (id < 0 || id >= B) continue;
+        const int off = gt_off[(int)id], cnt = gt_off[(int)id + 1] - off;
+        const int dst = sorted ? i : (off + rank[i]);
+        if (cnt > kContainMaxGt || risk[dst]) continue;
+        const float4 q = gt_box[dst];
+        bool inside = false;
+        for (int k = off; k < off + cnt; ++k) {
+            const float4 o = gt_box[k];
+            inside |= (k != dst) && o.x <= q.x && o.y <= q.y && o.z >= q.z && o.w >= q.w;
+        }
+        if (inside) {
+            risk[dst] = 1;
+            if (B <= kOrderMaxB) atomicAdd(&s_weight[(int)id], 1);
+        }
     }
     // Launch order of the images in k_assign (blockIdx.y -> image): the ones whose forced-assignment fix-up is
     // likely to have work first, so that those fix-ups run under the scan of the remaining images instead of
@@ -518,13 +539,15 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
     YS_REQUIRE(nc >= 1, YS_ERR_BAD_ARG, "nc must be >= 1");
     L.n = n_levels;
     L.C = 4 * reg_max + nc;
-    int a = 0, ch = 0, sg = 0, hs16 = 0;
+    int a = 0, ch = 0, sg = 0, hs16 = 0, sb = 0;
     for (int i = 0; i < n_levels; ++i) {
         YS_REQUIRE(xs[i] != nullptr && hs[i] > 0 && ws[i] > 0, YS_ERR_BAD_ARG, "level %d: null pointer or empty shape", i);
         YS_REQUIRE(((uintptr_t)xs[i] & 15) == 0, YS_ERR_BAD_ARG, "level %d: pointer must be 16-byte aligned", i);
         YS_REQUIRE((hs[i] * ws[i]) % 4 == 0, YS_ERR_UNSUPPORTED, "level %d: h*w must be a multiple of 4 (float4 path)", i);
         L.seg_off[i] = sg;
         L.hseg_off[i] = hs16;
+        L.sblk_off[i] = sb;
+        sb += (hs[i] * ws[i] + kScanThreads - 1) / kScanThreads;
         hs16 += (hs[i] * ws[i] + kBoxItem - 1) / kBoxItem;
         sg += (hs[i] * ws[i] + kSeg - 1) / kSeg;
         L.x[i] = xs[i];
@@ -538,12 +561,13 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
         a += L.hw[i];
         ch += (L.hw[i] + kChunk - 1) / kChunk;
     }
-    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.chunk_off[i] = ch; L.seg_off[i] = sg; L.hseg_off[i] = hs16; }
+    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.chunk_off[i] = ch; L.seg_off[i] = sg; L.hseg_off[i] = hs16; L.sblk_off[i] = sb; }
     for (int i = n_levels; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; }
     L.A = a;
     L.n_chunks = ch;
     L.n_segs = sg;
     L.n_hsegs = hs16;
+    L.n_sblk = sb;
     return YS_OK;
 }
 
@@ -551,7 +575,7 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static int build_stream_maps(StreamMaps &M, const LevelSet &L, int B) {
+static int get_encoder(EncodeTiledFn &out) {
     static EncodeTiledFn encode = nullptr;
     if (!encode) {
         void *fn = nullptr;
@@ -561,6 +585,30 @@ static int build_stream_maps(StreamMaps &M, const LevelSet &L, int B) {
                    "cuTensorMapEncodeTiled is not available from this driver");
         encode = (EncodeTiledFn)fn;
     }
+    out = encode;
+    return YS_OK;
+}
+static int build_scan_maps(ScanMaps &M, const LevelSet &L, int B) {
+    EncodeTiledFn encode;
+    int rc = get_encoder(encode);
+    if (rc) return rc;
+    memset(&M, 0, sizeof(M));
+    for (int l = 0; l < L.n; ++l) {
+        const cuuint64_t gdim[2] = {(cuuint64_t)L.hw[l], (cuuint64_t)B * (cuuint64_t)L.C};
+        const cuuint64_t gstride[1] = {(cuuint64_t)L.hw[l] * 4u};
+        const cuuint32_t estr[2] = {1u, 1u};
+        const cuuint32_t box[2] = {(cuuint32_t)kScanThreads, 64u};
+        CUresult r = encode(&M.lvl[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)L.x[l], gdim, gstride, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        YS_REQUIRE(r == CUDA_SUCCESS, YS_ERR_BAD_ARG, "tensor map (scan) of level %d: CUresult %d", l, (int)r);
+    }
+    return YS_OK;
+}
+static int build_stream_maps(StreamMaps &M, const LevelSet &L, int B) {
+    EncodeTiledFn encode;
+    int rc0 = get_encoder(encode);
+    if (rc0) return rc0;
     memset(&M, 0, sizeof(M));
     for (int l = 0; l < L.n; ++l) {
         const cuuint64_t gdim[2] = {(cuuint64_t)L.hw[l], (cuuint64_t)B * (cuuint64_t)L.C};
@@ -590,7 +638,7 @@ struct LossWorkspace {
     size_t bytes;
 };
 
-static inline int scan_blocks(int A) { return (A + kScanThreads - 1) / kScanThreads; }
+static inline int scan_blocks(int A) { return (A + kScanThreads - 1) / kScanThreads + YS_MAX_LEVELS; }   // upper bound (per-level cut)
 static inline size_t loss_items_bound(int B, int A, int nc) {
     const size_t per_img = (size_t)A / kSeg + YS_MAX_LEVELS + ((size_t)A / kChunk + YS_MAX_LEVELS) * ((nc + kClsGroup - 1) / kClsGroup);
     return (size_t)B * per_img;
@@ -680,8 +728,15 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     io.nc = nc; io.alpha = alpha; io.beta = beta; io.eps = 1e-9f;
 
     if (stages & YS_STAGE_ASSIGN) {
-        dim3 gs(scan_blocks(L.A), B);
-        k_assign<true><<<gs, kScanThreads, 0, stream>>>(L, io, B);
+        ScanMaps SM;
+        rc = build_scan_maps(SM, L, B);
+        if (rc) return rc;
+        const size_t smem = (size_t)kScanTileBytes + sizeof(AssignSmem);
+        cudaError_t ce = cudaFuncSetAttribute(k_assign<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        YS_REQUIRE(ce == cudaSuccess, (int)ce, "k_assign smem opt-in: %s", cudaGetErrorString(ce));
+        cudaFuncSetAttribute(k_assign<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        dim3 gs(L.n_sblk, B);
+        k_assign<true><<<gs, kScanThreads, smem, stream>>>(L, io, B, SM);
         YS_CHECK_LAUNCH("k_assign");
     }
 
@@ -803,8 +858,8 @@ extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, co
     LevelSet L;
     L.n = 1; L.A = A; L.C = nc; L.n_chunks = 0;
     for (int i = 0; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; }
-    for (int i = 0; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = i == 0 ? 0 : A; L.chunk_off[i] = 0; L.seg_off[i] = 0; L.hseg_off[i] = 0; }
-    L.n_segs = 0; L.n_hsegs = 0;
+    for (int i = 0; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = i == 0 ? 0 : A; L.chunk_off[i] = 0; L.seg_off[i] = 0; L.hseg_off[i] = 0; L.sblk_off[i] = 0; }
+    L.n_segs = 0; L.n_hsegs = 0; L.n_sblk = 0;
 
     AssignIO io;
     io.gt_off = nullptr; io.G = G; io.gt_box = (const float4 *)gt_bboxes; io.gt_label_i = nullptr;
@@ -816,8 +871,10 @@ extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, co
     io.done_counter = W.counters; io.img_done = W.counters + 2;
     io.nc = nc; io.alpha = alpha; io.beta = beta; io.eps = eps;
 
-    dim3 gs(scan_blocks(A), B);
-    k_assign<false><<<gs, kScanThreads, 0, stream>>>(L, io, B);
+    ScanMaps SM;
+    memset(&SM, 0, sizeof(SM));
+    dim3 gs((A + kScanThreads - 1) / kScanThreads, B);
+    k_assign<false><<<gs, kScanThreads, sizeof(AssignSmem), stream>>>(L, io, B, SM);
     YS_CHECK_LAUNCH("k_assign(dense)");
     const size_t tot = (size_t)B * A;
     k_assign_emit<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(B, A, G, nc, W.tgi, io.norm, gt_labels,
