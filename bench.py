@@ -13,7 +13,8 @@ One JSON line on rank 0:
              backward, gradients written) on inputs resident in HBM, timed with CUDA events, max over ranks.
   e2e        the same metric through the drop-in Python API (v8DetectionLoss.__call__ + backward) with the
              head tensors and targets coming from pinned HOST memory each step and the loss items read back.
-  roofline   the dominant kernel (k_loss) re-launched alone over its own timed region:
+  roofline   the dominant kernel (k_loss_stream) timed in place: the step launched stage by stage with a CUDA
+             event between the kernels;
              algorithmic bytes (2 * A * (4*reg_max+nc) * 4 per image) / CUDA-event time vs MEASURED_PEAKS.json.
   cpu_baseline  the oracle port of the reference's PyTorch path (oracle/ref_port.py) on the host cores.
   nms        side measurement of configs[3] (batched NMS, B=256, conf 0.001 / IoU 0.7), N=1 only.
@@ -220,11 +221,18 @@ def run_b200(args):
         return float(t.item())
 
     # ---- value: K steps of the C-ABI call on resident inputs
+    sampler = ClockSampler(local)
+    sampler.start()
     for _ in range(max(args.warmup, 3)):
         call()
-    sampler = ClockSampler(local)
+    # clock settle: the step is ~0.2 ms, so W steps alone neither bring the SM clock up from idle nor give
+    # nvidia-smi (200 ms period) a sample under load; ~0.6 s of extra untimed steps do both
+    t_settle = time.perf_counter()
+    while time.perf_counter() - t_settle < 0.6:
+        for _ in range(50):
+            call()
+        torch.cuda.synchronize(dev)
     barrier()
-    sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(args.steps):
@@ -235,41 +243,35 @@ def run_b200(args):
     value = world * B_PER_GPU * args.steps / (ms_total * 1e-3)
     loss_vec = out.tolist()
 
-    # ---- roofline: the dominant kernel alone, re-launched over its own timed region (state from the last full call)
+    # ---- roofline: the same step, launched stage by stage with a CUDA event between the kernels, so that every
+    #      kernel is timed where it runs in the pipeline (a kernel re-launched back to back with itself starts on an
+    #      L2 full of its own dirty gradient lines and reads ~15 % slower than it does after k_assign).
     reps = max(args.steps, 20)
+    names = (("k_pack_gt", 1), ("k_assign", 2), ("k_loss_stream", 4))
     for _ in range(3):
-        call(4)
-    torch.cuda.synchronize(dev)
-    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    k0.record(stream)
-    for _ in range(reps):
-        call(4)
-    k1.record(stream)
-    torch.cuda.synchronize(dev)
-    loss_ms = k0.elapsed_time(k1) / reps
-    # per-stage breakdown (each stage timed alone the same way)
-    stage_ms = {}
-    for name, bit in (("k_pack_gt", 1), ("k_assign", 2), ("k_loss", 4)):
-        call()
-        torch.cuda.synchronize(dev)
-        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a0.record(stream)
-        for _ in range(10):
+        for _, bit in names:
             call(bit)
-        a1.record(stream)
-        torch.cuda.synchronize(dev)
-        stage_ms[name] = a0.elapsed_time(a1) / 10
-    clocks = sampler.stop()
+    torch.cuda.synchronize(dev)
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(reps)]
+    for r in range(reps):
+        evs[r][0].record(stream)
+        for k, (_, bit) in enumerate(names):
+            call(bit)
+            evs[r][k + 1].record(stream)
+    torch.cuda.synchronize(dev)
+    stage_ms = {name: sum(evs[r][k].elapsed_time(evs[r][k + 1]) for r in range(reps)) / reps
+                for k, (name, _) in enumerate(names)}
+    loss_ms = stage_ms["k_loss_stream"]
     peak, peak_src = peaks()
     achieved = ALG_BYTES_PER_IMG * B_PER_GPU / (loss_ms * 1e-3) / 1e9
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get("k_loss_dram_bytes_per_launch")
+            traffic = json.load(open(tp)).get("k_loss_stream_dram_bytes_per_launch")
         except Exception:
             traffic = None
-    roofline = {"bound": "hbm", "kernel": "k_loss", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "k_loss_stream", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms": loss_ms, "algorithmic_bytes_per_launch": ALG_BYTES_PER_IMG * B_PER_GPU,
                 "whole_step_achieved_gbs_per_gpu": ALG_BYTES_PER_IMG * B_PER_GPU * args.steps / (ms_total * 1e-3) / 1e9,
@@ -296,6 +298,7 @@ def run_b200(args):
     g1.record(stream)
     barrier()
     e2e_ms = max_over_ranks(g0.elapsed_time(g1))
+    clocks = sampler.stop()
     h2d = sum(f.numel() * 4 for f in feats_h) + sum(v.numel() * v.element_size() for v in batch_h.values())
     e2e = {"value": world * B_PER_GPU * e2e_steps / (e2e_ms * 1e-3), "unit": "images/s", "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": 16, "steps": e2e_steps,

@@ -575,6 +575,22 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+// Dynamic shared-memory opt-in of a kernel, once per device (the attribute is sticky; repeating the call on every
+// launch costs host time for nothing).  Not state that results depend on.
+template <typename K>
+static int optin_smem(K kernel, size_t bytes, unsigned long long &done_mask, const char *what) {
+    int dev = 0;
+    cudaError_t ce = cudaGetDevice(&dev);
+    YS_REQUIRE(ce == cudaSuccess, (int)ce, "%s: cudaGetDevice: %s", what, cudaGetErrorString(ce));
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (done_mask & bit) return YS_OK;
+    ce = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    YS_REQUIRE(ce == cudaSuccess, (int)ce, "%s smem opt-in: %s", what, cudaGetErrorString(ce));
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    done_mask |= bit;
+    return YS_OK;
+}
+
 static int get_encoder(EncodeTiledFn &out) {
     static EncodeTiledFn encode = nullptr;
     if (!encode) {
@@ -732,9 +748,9 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         rc = build_scan_maps(SM, L, B);
         if (rc) return rc;
         const size_t smem = (size_t)kScanTileBytes + sizeof(AssignSmem);
-        cudaError_t ce = cudaFuncSetAttribute(k_assign<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        YS_REQUIRE(ce == cudaSuccess, (int)ce, "k_assign smem opt-in: %s", cudaGetErrorString(ce));
-        cudaFuncSetAttribute(k_assign<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        static unsigned long long optin_assign = 0ull;
+        rc = optin_smem(k_assign<true>, smem, optin_assign, "k_assign");
+        if (rc) return rc;
         dim3 gs(L.n_sblk, B);
         k_assign<true><<<gs, kScanThreads, smem, stream>>>(L, io, B, SM);
         YS_CHECK_LAUNCH("k_assign");
@@ -761,13 +777,14 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         StreamMaps M;
         rc = build_stream_maps(M, L, B);
         if (rc) return rc;
+        static unsigned long long optin_t = 0ull, optin_f = 0ull;
         if (level_grad_host) {
-            ce = cudaFuncSetAttribute(k_loss_stream<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            YS_REQUIRE(ce == cudaSuccess, (int)ce, "k_loss_stream smem opt-in: %s", cudaGetErrorString(ce));
+            rc = optin_smem(k_loss_stream<true>, smem, optin_t, "k_loss_stream");
+            if (rc) return rc;
             k_loss_stream<true><<<blocks, kStreamThreads, smem, stream>>>(L, P, M);
         } else {
-            ce = cudaFuncSetAttribute(k_loss_stream<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            YS_REQUIRE(ce == cudaSuccess, (int)ce, "k_loss_stream smem opt-in: %s", cudaGetErrorString(ce));
+            rc = optin_smem(k_loss_stream<false>, smem, optin_f, "k_loss_stream(fwd)");
+            if (rc) return rc;
             k_loss_stream<false><<<blocks, kStreamThreads, smem, stream>>>(L, P, M);
         }
         YS_CHECK_LAUNCH("k_loss_stream");
