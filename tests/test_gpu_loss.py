@@ -73,20 +73,35 @@ def test_loss_golden_c1(cuda_lib, name):
     (202, 3, 40, {"p_empty": 0.34, "p_nested": 0.3}),
 ])
 def test_loss_vs_oracle_640_with_spliced_assignment(cuda_lib, seed, B, max_gt, kw):
+    spliced_case(seed, B, 640, max_gt, kw)
+
+
+@pytest.mark.parametrize("seed,B,imgsz,kw", [
+    # BASELINE.json configs[4] shape: 1280 px (A = 33600), exactly 300 GT per image -- more GT than one shared-memory
+    # tile (256) holds, so the multi-tile scan and the global-scratch fix-up run; many GT own nothing (loop 2)
+    (210, 1, 1280, {"fixed_count": 300, "dense": True}),
+    # same GT density on a small image: almost every GT is at risk or forced
+    (211, 2, 320, {"fixed_count": 300, "dense": True, "p_tiny": 0.1, "p_nested": 0.2}),
+    (212, 2, 320, {"fixed_count": 70, "p_tiny": 0.2, "p_nested": 0.3}),     # just above the containment-hint limit (64)
+])
+def test_loss_dense_scene_vs_oracle(cuda_lib, seed, B, imgsz, kw):
+    spliced_case(seed, B, imgsz, kw.get("fixed_count", 20), kw)
+
+
+def spliced_case(seed, B, imgsz, max_gt, kw):
     from oracle import ref_port as orc
-    feats = synth.make_head_levels(B, 640, 80, 16, seed=seed)
-    batch = synth.make_gt_batch(B, 80, max_gt, seed=seed + 1, **kw)
+    feats = synth.make_head_levels(B, imgsz, 80, 16, seed=seed)
+    batch = synth.make_gt_batch(B, 80, max_gt, seed=seed + 1, imgsz=imgsz, **kw)
     total, items, grads, crit = run_cuda(feats, batch, 80, export=True)
     leaves = [f.clone().requires_grad_(True) for f in feats]
     rtotal, ritems, parts = orc.detection_loss(leaves, batch, 80, 16, synth.LEVEL_STRIDES, return_parts=True)
     rtotal.backward()
     ex = {k: v.cpu() for k, v in crit.last_export.items()}
     # (1) decoded boxes to 1e-6 of the image size
-    assert (ex["pred_bboxes_px"] - parts["pred_bboxes_px"]).abs().max().item() <= 1e-6 * 640 * 4
+    assert (ex["pred_bboxes_px"] - parts["pred_bboxes_px"]).abs().max().item() <= 1e-6 * imgsz * 4
     # (2) spliced oracle: the oracle assigner fed with OUR decoded boxes must give OUR indices bit-exactly
     A = ex["pred_bboxes_px"].shape[1]
-    imgsz = torch.tensor([640.0, 640.0])
-    tg = orc.pack_targets(batch["cls"], batch["bboxes"], batch["batch_idx"], B, imgsz)
+    tg = orc.pack_targets(batch["cls"], batch["bboxes"], batch["batch_idx"], B, torch.tensor([float(imgsz), float(imgsz)]))
     anc, st = orc.anchors_for([f.shape[2:] for f in feats], synth.LEVEL_STRIDES)
     flat = torch.cat([f.view(B, 144, -1) for f in feats], 2)
     scores = flat[:, 64:].permute(0, 2, 1).sigmoid()

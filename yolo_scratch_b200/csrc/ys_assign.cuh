@@ -27,7 +27,10 @@ namespace ys {
 #endif
 constexpr int kScanThreads = YS_SCAN_THREADS;
 constexpr int kGtTile = 256;        // GT boxes staged per shared-memory tile
-constexpr int kFixSmemGt = 256;     // per-image GT count the fix-up handles with shared-memory scratch
+constexpr int kFixSmemGt = 256;     // per-image GT count the fix-up handles with shared-memory scratch (dense entry point)
+constexpr int kFixSmemGtFused = 1536;   // same, fused path: the fix-up scratch lives in the (consumed) 64 KB TMA tile
+constexpr float kDflReach = 15.5f;  // a decoded side is an expectation over bins 0..15: a predicted box reaches at most
+                                    // 15 cells from its anchor centre (0.5 cell of slack for the approximate softmax)
 constexpr int kScanTileBytes = 64 * kScanThreads * 4;   // fused path: 64 box channels x 256 anchors, one TMA operation
 
 // Fused path: one 2-D tensor map per level over [B*C rows][h*w columns] fp32, box {kScanThreads columns, 64 rows}.
@@ -52,7 +55,6 @@ struct AssignIO {
     int *owned_cnt;
     int *gt_flags;              // 1: some anchor centre lies inside
     const int *img_order;       // fused only (else nullptr): blockIdx.y -> image, a scheduling hint from k_pack_gt
-    const unsigned char *risk;  // fused only (else nullptr): GT whose best-IoU anchor the scan computes (hint from k_pack_gt)
     int skip_fixup;             // profiling only
     unsigned long long *best_key;   // per-GT arg-max key over all anchors: written by the scan for risk GT (zero on
                                     // entry), by the fix-up for the others when an image has more than kFixSmemGt GT
@@ -190,8 +192,7 @@ struct ScanSmem {
     float area[kGtTile];
     int any[kGtTile];
     int own[kGtTile];
-    unsigned long long rkey[kGtTile];   // arg-max keys of the tile's risk GT, indexed like rlist
-    unsigned short rlist[kGtTile];      // tile-relative indices of the risk GT
+    unsigned long long rkey[kGtTile];   // fused: this block's arg-max key (best IoU, lowest anchor) per GT of the tile; 0 = none
     unsigned char valid[kGtTile];
 };
 struct FixSmem {
@@ -209,7 +210,7 @@ union AssignSmem {
 };
 
 template <bool FUSED>
-__device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, FixSmem &S, int nblk);
+__device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, void *scratch, int cap, int nblk);
 
 template <bool FUSED>
 __global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS)
@@ -219,7 +220,7 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     AssignSmem &sm = *reinterpret_cast<AssignSmem *>(s_dyn + (FUSED ? kScanTileBytes : 0));
     __shared__ __align__(8) unsigned long long s_mbar;
     __shared__ float s_red[kScanThreads / 32];
-    __shared__ int s_flag, s_nrisk;
+    __shared__ int s_flag;
     ScanSmem &S = sm.s;
 
     const int b = (FUSED && io.img_order) ? io.img_order[blockIdx.y] : (int)blockIdx.y;
@@ -252,25 +253,20 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     gt_range<FUSED>(io, b, g0, n);
     const int ntiles = (n + kGtTile - 1) / kGtTile;
     const bool one_tile = ntiles <= 1;
-    if (tid == 0) s_nrisk = 0;
     // GT tile -> shared memory (no barriers inside; the caller brackets it)
-    auto stage_gt = [&](int t0, int tn, bool register_risk) {
+    auto stage_gt = [&](int t0, int tn) {
         for (int j = tid; j < tn; j += kScanThreads) {
             const float4 q = io.gt_box[g0 + t0 + j];
             S.box[j] = q;
             S.area[j] = area_eps_h(q.x, q.y, q.z, q.w);
             S.any[j] = 0;
             S.own[j] = 0;
+            S.rkey[j] = 0ull;
             S.valid[j] = FUSED ? 1 : (io.gt_valid[g0 + t0 + j] != 0.f);
-            if (FUSED && register_risk && io.risk[g0 + t0 + j]) {
-                const int r = atomicAdd(&s_nrisk, 1);
-                S.rlist[r] = (unsigned short)j;
-                S.rkey[r] = 0ull;
-            }
         }
     };
-    __syncthreads();               // s_nrisk reset and (fused) mbarrier initialised
-    if (ntiles > 0) stage_gt(0, min(kGtTile, n), true);      // overlaps the tile load of the fused path
+    __syncthreads();               // (fused) mbarrier initialised
+    if (ntiles > 0) stage_gt(0, min(kGtTile, n));            // overlaps the tile load of the fused path
     __syncthreads();
 
     // ---- this anchor's predicted box (px) and centre (px)
@@ -326,71 +322,114 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     int cnt = 0, first = -1, best_g = 0;
     float best_ov = -1.f;
 
-    // ---- pass 0: centre-in-box per GT (losses/yolo_v8_loss.py:210-224); pass 1: IoU arg-max for multi-hit anchors
-    for (int pass = 0; pass < 2; ++pass) {
+    // Warp-level prefilter of pass 0: lane j asks whether GT j can contain ANY of the warp's anchor centres (their
+    // bounding box); the exact per-anchor test then runs over the few GT that pass, in ascending order.
+    auto pass0_tile = [&](int t0, int tn) {
+        for (int j0 = 0; j0 < tn; j0 += 32) {
+            const int jl = j0 + lane;
+            bool rel = false;
+            if (jl < tn && S.valid[jl]) {
+                const float4 q = S.box[jl];
+                rel = q.x < wx_max && q.z > wx_min && q.y < wy_max && q.w > wy_min;
+            }
+            unsigned m = __ballot_sync(0xffffffffu, rel);
+            while (m) {
+                const int j = j0 + __ffs(m) - 1;
+                m &= m - 1;
+                if (live && centre_in_box(ax, ay, S.box[j])) {
+                    if (first < 0) first = t0 + j;
+                    ++cnt;
+                    S.any[j] = 1;
+                }
+            }
+        }
+    };
+    if (FUSED) {
+        // ONE pass over the GT tiles.  After the centre-in-box test (:210-224) every GT within reach of this warp's
+        // anchors -- a decoded box extends at most kDflReach cells from its centre, so IoU(anchor, GT) is exactly 0
+        // outside that window -- gets its IoU evaluated once, serving both
+        //   * the anchor's own arg-max over all GT slots (:226-244, used if it sits in more than one GT), and
+        //   * the GT's arg-max over all anchors (:136, :156, what the forced-assignment loops ask for): redux.max on
+        //     the IoU bits (>= 0, so they order as integers), lowest lane among the ties, one shared atomicMax per warp.
+        //     Keys with IoU 0 are never recorded: k_pack_gt preset every key to (IoU 0, anchor 0), the first maximum
+        //     of an all-zero column.
+        const float reach = kDflReach * L.stride[lvl];
+        const float rx0 = wx_min - reach, rx1 = wx_max + reach, ry0 = wy_min - reach, ry1 = wy_max + reach;
+        const bool warp_live = __any_sync(0xffffffffu, live);
         for (int t = 0; t < ntiles; ++t) {
             const int t0 = t * kGtTile;
             const int tn = min(kGtTile, n - t0);
-            if ((pass == 0 && t > 0) || (pass == 1 && !one_tile)) {       // tile 0 of pass 0 was staged above
+            if (t > 0) {                                          // tile 0 was staged above
                 __syncthreads();
-                if (tid == 0) s_nrisk = 0;
-                __syncthreads();
-                stage_gt(t0, tn, pass == 0);
+                stage_gt(t0, tn);
                 __syncthreads();
             }
-            if (pass == 0) {
-                // Warp-level prefilter: lane j asks whether GT j can contain ANY of the warp's anchor centres (their
-                // bounding box, by redux on the float bits -- centres are positive); the exact per-anchor test then
-                // runs over the few GT that pass, in ascending order.
+            pass0_tile(t0, tn);
+            if (warp_live) {
                 for (int j0 = 0; j0 < tn; j0 += 32) {
                     const int jl = j0 + lane;
                     bool rel = false;
-                    if (jl < tn && S.valid[jl]) {
+                    if (jl < tn) {
                         const float4 q = S.box[jl];
-                        rel = q.x < wx_max && q.z > wx_min && q.y < wy_max && q.w > wy_min;
+                        rel = q.x < rx1 && q.z > rx0 && q.y < ry1 && q.w > ry0;
                     }
                     unsigned m = __ballot_sync(0xffffffffu, rel);
                     while (m) {
                         const int j = j0 + __ffs(m) - 1;
                         m &= m - 1;
-                        if (live && centre_in_box(ax, ay, S.box[j])) {
-                            if (first < 0) first = t0 + j;
-                            ++cnt;
-                            S.any[j] = 1;
+                        const float ovr = live ? iou_assign_lazy(p, area_p, S.box[j], S.area[j]) : 0.f;
+                        if (ovr > best_ov) { best_ov = ovr; best_g = t0 + j; }    // first maximum (ascending j)
+                        const unsigned bits = __float_as_uint(ovr);
+                        const unsigned mx = __reduce_max_sync(0xffffffffu, bits);
+                        if (mx != 0u) {
+                            const unsigned who = __ballot_sync(0xffffffffu, bits == mx);
+                            if (lane == __ffs(who) - 1) atomicMax(&S.rkey[j], argmax_key(ovr, (unsigned)a));
                         }
                     }
                 }
-                // risk GT: arg-max over all anchors of IoU(anchor, GT), first maximum (:136, :156) -- this block's
-                // share.  Warp: redux.max on the IoU bits (>= 0, so they order as integers), lowest lane among the ties.
-                const int nrisk = FUSED ? s_nrisk : 0;
-                if (nrisk > 0 && __any_sync(0xffffffffu, live)) {     // warp-uniform
-                    for (int r = 0; r < nrisk; ++r) {
-                        const int j = S.rlist[r];
-                        const float ovr = live ? iou_assign_lazy(p, area_p, S.box[j], S.area[j]) : 0.f;
-                        const unsigned bits = __float_as_uint(ovr);
-                        const unsigned mx = __reduce_max_sync(0xffffffffu, bits);
-                        const unsigned who = __ballot_sync(0xffffffffu, bits == mx);
-                        if (lane == __ffs(who) - 1) atomicMax(&S.rkey[r], argmax_key(ovr, (unsigned)a));
-                    }
-                }
-                if (!one_tile) {
-                    __syncthreads();
-                    for (int j = tid; j < tn; j += kScanThreads)
-                        if (S.any[j]) io.gt_flags[g0 + t0 + j] = 1;
-                    for (int r = tid; r < nrisk; r += kScanThreads) atomicMax(&io.best_key[g0 + t0 + S.rlist[r]], S.rkey[r]);
-                }
-            } else if (cnt > 1) {
-                for (int j = 0; j < tn; ++j) {
-                    const float ov = iou_assign_lazy(p, area_p, S.box[j], S.area[j]);
-                    if (ov > best_ov) { best_ov = ov; best_g = t0 + j; }     // first maximum over ALL slots (:233)
+            }
+            if (!one_tile) {
+                __syncthreads();
+                for (int j = tid; j < tn; j += kScanThreads) {
+                    if (S.any[j]) io.gt_flags[g0 + t0 + j] = 1;
+                    if (S.rkey[j]) atomicMax(&io.best_key[g0 + t0 + j], S.rkey[j]);
                 }
             }
         }
-        // pass 1 only where some anchor sits in more than one GT: per warp when the GT are already staged,
-        // per block when pass 1 has to re-stage tiles
-        if (pass == 0) {
-            if (one_tile) { if (!__any_sync(0xffffffffu, cnt > 1)) break; }
-            else if (!__syncthreads_or(cnt > 1)) break;
+        // all slots outside the window (and possibly some inside) have IoU 0: the first maximum of an all-zero row is slot 0
+        if (!(best_ov > 0.f)) { best_ov = 0.f; best_g = 0; }
+    } else {
+        // dense entry point: arbitrary predicted boxes, no reach bound.  Pass 0: centre-in-box; pass 1: IoU arg-max over
+        // all GT slots for anchors inside more than one GT (the forced-assignment arg-max is left to the fix-up).
+        for (int pass = 0; pass < 2; ++pass) {
+            for (int t = 0; t < ntiles; ++t) {
+                const int t0 = t * kGtTile;
+                const int tn = min(kGtTile, n - t0);
+                if ((pass == 0 && t > 0) || (pass == 1 && !one_tile)) {       // tile 0 of pass 0 was staged above
+                    __syncthreads();
+                    stage_gt(t0, tn);
+                    __syncthreads();
+                }
+                if (pass == 0) {
+                    pass0_tile(t0, tn);
+                    if (!one_tile) {
+                        __syncthreads();
+                        for (int j = tid; j < tn; j += kScanThreads)
+                            if (S.any[j]) io.gt_flags[g0 + t0 + j] = 1;
+                    }
+                } else if (cnt > 1) {
+                    for (int j = 0; j < tn; ++j) {
+                        const float ov = iou_assign_lazy(p, area_p, S.box[j], S.area[j]);
+                        if (ov > best_ov) { best_ov = ov; best_g = t0 + j; }     // first maximum over ALL slots (:233)
+                    }
+                }
+            }
+            // pass 1 only where some anchor sits in more than one GT: per warp when the GT are already staged,
+            // per block when pass 1 has to re-stage tiles
+            if (pass == 0) {
+                if (one_tile) { if (!__any_sync(0xffffffffu, cnt > 1)) break; }
+                else if (!__syncthreads_or(cnt > 1)) break;
+            }
         }
     }
 
@@ -425,9 +464,8 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         for (int j = tid; j < n; j += kScanThreads) {
             if (S.own[j]) atomicAdd(&io.owned_cnt[g0 + j], S.own[j]);
             if (S.any[j]) io.gt_flags[g0 + j] = 1;
+            if (FUSED && S.rkey[j]) atomicMax(&io.best_key[g0 + j], S.rkey[j]);
         }
-        if (FUSED)
-            for (int r = tid; r < s_nrisk; r += kScanThreads) atomicMax(&io.best_key[g0 + S.rlist[r]], S.rkey[r]);
     }
     if (tid == 0) {
         float tsum = 0.f;
@@ -450,7 +488,9 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         if (tid == 0) io.img_done[b] = 0u;
         return;
     }
-    fixup_image<FUSED>(L, io, b, B, sm.f, (int)gridDim.x);
+    // fix-up scratch: fused -- the 64 KB tile (consumed by the decode above); dense -- the scan's own shared memory
+    if (FUSED) fixup_image<FUSED>(L, io, b, B, s_dyn, kFixSmemGtFused, (int)gridDim.x);
+    else fixup_image<FUSED>(L, io, b, B, &sm.f, kFixSmemGt, (int)gridDim.x);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -489,7 +529,7 @@ __device__ __forceinline__ void fix_argmax(const LevelSet &L, const AssignIO &io
 }
 
 template <bool FUSED>
-__device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, FixSmem &S, int nblk) {
+__device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, void *scratch, int cap, int nblk) {
     __shared__ int s_nneedy, s_ncmp, s_nlost, s_resume, s_nfired, s_want;
     __shared__ double s_delta[kScanThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -500,15 +540,17 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
     int *labp = io.lab ? io.lab + (size_t)b * L.A : nullptr;
     volatile float *norm = io.norm + (size_t)b * L.A;
     // per-GT scratch: shared memory when the image's GT fit, else the global scratch (8 ints per GT) in place
-    const bool in_smem = n <= kFixSmemGt;
+    const bool in_smem = n <= cap;
+    unsigned long long *s_key = reinterpret_cast<unsigned long long *>(scratch);      // [cap], then 7 int arrays of cap
+    int *s_int = reinterpret_cast<int *>(s_key + cap);
     int *gs = io.forced + 8 * (size_t)g0;
-    int *cntp = in_smem ? S.cnt : (io.owned_cnt + g0);
-    int *forced = in_smem ? S.forced : gs;                         // [2j] loop-1 anchor, [2j+1] loop-2 anchor
-    int *needy = in_smem ? S.needy : (gs + 2 * (size_t)n);         // GT whose arg-max anchor is needed
-    int *kk = in_smem ? S.kk : (gs + 3 * (size_t)n);               // arg-max anchor of GT j (-1: not computed)
-    int *tg0 = in_smem ? S.tg0 : (gs + 4 * (size_t)n);             // owner GT of anchor kk[j] after phase 1
-    int *lost = in_smem ? S.lost : (gs + 5 * (size_t)n);
-    unsigned long long *keyp = in_smem ? S.key : (io.best_key + g0);
+    int *cntp = in_smem ? s_int : (io.owned_cnt + g0);
+    int *forced = in_smem ? s_int + cap : gs;                               // [2j] loop-1 anchor, [2j+1] loop-2 anchor
+    int *needy = in_smem ? s_int + 3 * cap : (gs + 2 * (size_t)n);          // GT whose arg-max anchor is needed
+    int *kk = in_smem ? s_int + 4 * cap : (gs + 3 * (size_t)n);             // arg-max anchor of GT j (-1: not computed)
+    int *tg0 = in_smem ? s_int + 5 * cap : (gs + 4 * (size_t)n);            // owner GT of anchor kk[j] after phase 1
+    int *lost = in_smem ? s_int + 6 * cap : (gs + 5 * (size_t)n);
+    unsigned long long *keyp = in_smem ? s_key : (io.best_key + g0);
 
     if (tid == 0) { s_nneedy = 0; s_ncmp = 0; s_nlost = 0; }
     if (tid < kWarps) s_delta[tid] = 0.0;
@@ -518,12 +560,12 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
         const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
         const int c = __ldcg(io.owned_cnt + g0 + j);
         const int fl = __ldcg(io.gt_flags + g0 + j);
-        if (in_smem) S.cnt[j] = c;
+        if (in_smem) cntp[j] = c;
         const bool lonely1 = valid && fl == 0;           // loop 1 (:117-139): valid GT with no anchor centre inside
         forced[2 * j] = lonely1 ? -2 : -1;               // -2: pending, resolved below
         forced[2 * j + 1] = -1;
         // risk GT: the scan already found the arg-max anchor (all blocks of the image are done: key is final)
-        const bool have = FUSED && io.risk != nullptr && io.risk[g0 + j];
+        const bool have = FUSED;      // fused: the scan left every GT's arg-max key in best_key (all blocks are done)
         const unsigned long long key = have ? __ldcg(io.best_key + g0 + j) : 0ull;
         if (in_smem || !have) keyp[j] = key;
         kk[j] = have ? (int)argmax_key_index(key) : -1;

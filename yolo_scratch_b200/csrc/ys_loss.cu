@@ -145,7 +145,7 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
     // placement
     const bool sorted = !s_unsorted;
     for (int i = tid; i < N; i += kPackThreads) {
-        best_key[i] = 0ull;
+        best_key[i] = 0xFFFFFFFFull;      // = argmax_key(IoU 0, anchor 0): the first maximum of an all-zero column
         owned_cnt[i] = 0;
         gt_flags[i] = 0;
         long long id = batch_idx[i];
@@ -278,7 +278,7 @@ k_pack_gt_small(LevelSet L, const long long *__restrict__ batch_idx, const long 
     const int excl = s_part[warp] + incl - cnt_b;
     if (tid < B) { s_off[tid] = excl; gt_off[tid] = excl; }
     if (tid == B - 1) { s_off[B] = excl + cnt_b; gt_off[B] = excl + cnt_b; }
-    if (tid < N) { best_key[tid] = 0ull; owned_cnt[tid] = 0; gt_flags[tid] = 0; }
+    if (tid < N) { best_key[tid] = 0xFFFFFFFFull; owned_cnt[tid] = 0; gt_flags[tid] = 0; }   // key (IoU 0, anchor 0)
     __syncthreads();
     // ---- placement, pixel scale (losses/yolo_v8_loss.py:515-516), risk hint from the anchor grid
     int dst = -1;
@@ -862,7 +862,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     io.gt_off = W.gt_off; io.G = 0; io.gt_box = W.gt_box; io.gt_label_i = W.gt_label; io.gt_label_f = nullptr;
     io.gt_valid = nullptr; io.pd_box = nullptr; io.pd_scores = nullptr; io.anc = nullptr;
     io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags; io.forced = W.forced;
-    io.img_order = W.img_order; io.risk = W.risk; io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
+    io.img_order = W.img_order; io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
     io.pbox = pred_boxes_px ? (float4 *)pred_boxes_px : W.pbox;
     io.tgi = target_gt_idx ? (int *)target_gt_idx : W.tgi;
     io.lab = W.lab;
@@ -1023,7 +1023,7 @@ extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, co
     io.gt_off = nullptr; io.G = G; io.gt_box = (const float4 *)gt_bboxes; io.gt_label_i = nullptr;
     io.gt_label_f = gt_labels; io.gt_valid = mask_gt; io.pd_box = (const float4 *)pd_bboxes; io.pd_scores = pd_scores;
     io.anc = (const float2 *)anc_points; io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags;
-    io.img_order = nullptr; io.risk = nullptr; io.skip_fixup = 0;
+    io.img_order = nullptr; io.skip_fixup = 0;
     io.forced = W.forced; io.pbox = nullptr; io.tgi = W.tgi; io.lab = nullptr; io.norm = norm_out ? norm_out : W.norm;
     io.partial = W.scan_partial; io.img_sum = W.img_sum; io.tss = W.tss;
     io.done_counter = W.counters; io.img_done = W.counters + 2;
