@@ -223,8 +223,14 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     __shared__ int s_flag;
     ScanSmem &S = sm.s;
 
-    const int b = (FUSED && io.img_order) ? io.img_order[blockIdx.y] : (int)blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (FUSED) {
+        // programmatic dependent launch: let k_loss_stream become resident behind this grid's last wave, and wait here
+        // for k_pack_gt (whose outputs -- image order, GT lists -- are read from the next line on)
+        cudaTriggerProgrammaticLaunchCompletion();
+        cudaGridDependencySynchronize();
+    }
+    const int b = (FUSED && io.img_order) ? io.img_order[blockIdx.y] : (int)blockIdx.y;
     // fused: blocks are cut per level (a block never straddles two levels: one tensor operation loads its tile)
     int lvl = 0, i_lvl = 0, a;
     bool live;

@@ -48,6 +48,7 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
     __shared__ int s_part[kPackThreads / 32];
     __shared__ int s_unsorted;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    cudaTriggerProgrammaticLaunchCompletion();      // k_assign may start its prologue (it waits for this grid to finish)
     volatile int *cursor = (B <= kPackSmemB) ? (volatile int *)s_cursor : (volatile int *)cursor_g;
     for (int i = tid; i < B; i += kPackThreads) cursor[i] = 0;
     for (int i = tid; i < n_counters; i += kPackThreads) counters[i] = 0u;    // arrival counters of k_assign / k_loss
@@ -224,6 +225,7 @@ k_pack_gt_small(LevelSet L, const long long *__restrict__ batch_idx, const long 
     __shared__ unsigned char s_risk[kSmallMax];
     __shared__ int s_part[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    cudaTriggerProgrammaticLaunchCompletion();      // k_assign may start its prologue (it waits for this grid to finish)
     // ---- the only global reads
     long long id64 = -1, c64 = 0;
     float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -713,6 +715,22 @@ static int optin_smem(K kernel, size_t bytes, unsigned long long &done_mask, con
     return YS_OK;
 }
 
+// Launch with programmatic dependent launch (PDL): the kernel may start while its predecessor in the stream is still
+// draining (the predecessor calls cudaTriggerProgrammaticLaunchCompletion() at its start, i.e. the dependent becomes
+// eligible once the predecessor's last wave is resident); the dependent runs its prologue and then blocks in
+// cudaGridDependencySynchronize() until the predecessor has completed and its writes are visible.  Hides the launch
+// latency and prologue of k_assign and k_loss_stream (3 launches per step, ~180 us per step).
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 static int get_encoder(EncodeTiledFn &out) {
     static EncodeTiledFn encode = nullptr;
     if (!encode) {
@@ -880,7 +898,8 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         rc = optin_smem(k_assign<true>, smem, optin_assign, "k_assign");
         if (rc) return rc;
         dim3 gs(L.n_sblk, B);
-        k_assign<true><<<gs, kScanThreads, smem, stream>>>(L, io, B, SM);
+        cudaError_t le = launch_pdl(k_assign<true>, gs, dim3(kScanThreads), smem, stream, L, io, B, SM);
+        YS_REQUIRE(le == cudaSuccess, (int)le, "k_assign launch: %s", cudaGetErrorString(le));
         YS_CHECK_LAUNCH("k_assign");
     }
 
@@ -922,11 +941,13 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         if (level_grad_host) {
             rc = optin_smem(k_loss_stream<true>, smem, optin_t, "k_loss_stream");
             if (rc) return rc;
-            k_loss_stream<true><<<blocks, kStreamThreads, smem, stream>>>(L, P, M);
+            cudaError_t le = launch_pdl(k_loss_stream<true>, dim3(blocks), dim3(kStreamThreads), smem, stream, L, P, M);
+            YS_REQUIRE(le == cudaSuccess, (int)le, "k_loss_stream launch: %s", cudaGetErrorString(le));
         } else {
             rc = optin_smem(k_loss_stream<false>, smem, optin_f, "k_loss_stream(fwd)");
             if (rc) return rc;
-            k_loss_stream<false><<<blocks, kStreamThreads, smem, stream>>>(L, P, M);
+            cudaError_t le = launch_pdl(k_loss_stream<false>, dim3(blocks), dim3(kStreamThreads), smem, stream, L, P, M);
+            YS_REQUIRE(le == cudaSuccess, (int)le, "k_loss_stream launch: %s", cudaGetErrorString(le));
         }
         YS_CHECK_LAUNCH("k_loss_stream");
     } else if (stages & YS_STAGE_LOSS) {

@@ -330,6 +330,8 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, S
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
 
+    // programmatic dependent launch: everything above ran while k_assign was still draining; its outputs are read from here on
+    cudaGridDependencySynchronize();
     const float inv_tss = 1.0f / P.tss[0];
     float acc_box = 0.f, acc_cls = 0.f, acc_dfl = 0.f;
     char *ring = s_ring + (size_t)warp * kStreamStages * kStageBytes;
