@@ -921,18 +921,24 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         const int want = (P.total_items + kStreamWarps - 1) / kStreamWarps;
         const unsigned blocks = (unsigned)(want < sms ? (want > 0 ? want : 1) : (sms > 4096 ? 4096 : sms));
         const size_t smem = (size_t)kStreamWarps * kStreamStages * kStageBytes;
-        {   // schedule permutation over groups of kStreamWarps items: multiplier near NG/golden-ratio, coprime with NG
-            const unsigned long long NG = ((unsigned long long)P.total_items + kStreamWarps - 1) / kStreamWarps;
-            unsigned long long m = (unsigned long long)((double)NG * 0.6180339887498949);
-            if (m < 1) m = 1;
-            auto gcd = [](unsigned long long a, unsigned long long b) { while (b) { unsigned long long t = a % b; a = b; b = t; } return a; };
-            while (gcd(m, NG) != 1) ++m;
-#ifndef YS_STREAM_PERM
-            m = 1;      // identity: a permuted walk measured 5-10 % slower (DRAM page locality across CTAs)
-#endif
+        {   // schedule (see k_loss_stream): rounds over contiguous windows of `blocks` groups, rotated per round so that a
+            // CTA's position inside an image drifts by ~0.382 of the image's items per round
+            const long long NG = ((long long)P.total_items + kStreamWarps - 1) / kStreamWarps;
+            const long long G = (long long)blocks, ipi = (long long)P.items_per_img;
             P.n_groups16 = (unsigned)NG;
-            P.perm_mul = (unsigned)(m % NG);
-            P.perm_step = (unsigned)(((unsigned long long)blocks % NG) * (m % NG) % NG);
+            P.rounds = (unsigned)((NG + G - 1) / G);
+            const long long d0 = (G * kStreamWarps) % ipi;                 // natural drift per round, in items
+#ifndef YS_STREAM_DRIFT
+#define YS_STREAM_DRIFT 0.5
+#endif
+            long long want_drift = (long long)(YS_STREAM_DRIFT * (double)ipi) - d0;
+            want_drift %= ipi;
+            if (want_drift < 0) want_drift += ipi;
+            long long r = (want_drift + kStreamWarps / 2) / kStreamWarps;   // rotation in groups
+#ifdef YS_STREAM_ROTATE
+            r = YS_STREAM_ROTATE;
+#endif
+            P.rotate = (unsigned)(G > 1 ? r % G : 0);
         }
         StreamMaps M;
         rc = build_stream_maps(M, L, B);

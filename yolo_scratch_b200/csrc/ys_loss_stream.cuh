@@ -8,7 +8,7 @@
 // mbarrier), so the tile of work item k+1 is in flight -- costing no registers -- while item k is computed:
 // 16 warps x 5 KB = 80 KB in flight per SM at all times.
 //
-//   grid      one CTA per SM (persistent), 16 warps; warp w of CTA c walks items c*16+w, +gridDim*16, ...
+//   grid      one CTA per SM (persistent), 12 warps (measured best of 8..20); rounds over contiguous windows of groups of 12 items
 //   items     image-major, per image first the box items, then the class items:
 //     box     16 anchors x 64 box channels (64 rows of 64 B).  Lane = (side pair, anchor): each half-warp runs two
 //             of the four sides, both halves evaluate the anchor's CIoU.  Items without a foreground anchor load
@@ -26,7 +26,7 @@
 namespace ys {
 
 #ifndef YS_STREAM_WARPS
-#define YS_STREAM_WARPS 16
+#define YS_STREAM_WARPS 12
 #endif
 constexpr int kStreamWarps = YS_STREAM_WARPS;
 constexpr int kStreamThreads = kStreamWarps * 32;
@@ -54,8 +54,8 @@ struct StreamParams {
     int items_per_img;       // n_box + n_chunks * n_groups
     int total_items;         // B * items_per_img
     unsigned n_groups16;     // groups of kStreamWarps consecutive items (one item per warp of a CTA)
-    unsigned perm_mul;       // schedule permutation over groups: a CTA's k-th group is (gidx * perm_mul) mod n_groups16
-    unsigned perm_step;      // (gridDim.x * perm_mul) mod n_groups16
+    unsigned rounds;         // ceil(n_groups16 / gridDim.x): every CTA runs this many rounds (groups past the end are padding)
+    unsigned rotate;         // per-round rotation of the CTA -> group map inside the round's window (see the kernel)
     float hyp_box, hyp_cls, hyp_dfl;
     float batch;
 };
@@ -110,9 +110,8 @@ __device__ __forceinline__ Item decode_item(const LevelSet &L, const StreamParam
     }
     it.b = item / P.items_per_img;
     const int r = item - it.b * P.items_per_img;
-    // Items of an image: first the box items, then the class items, and CTAs walk the items in order (see the
-    // schedule note in the kernel).  Measured alternatives -- box/class interleaved in proportion, per-item or per-group
-    // permuted walks -- all lose 4-10 %: the SMs sweeping ONE contiguous window of rows is what DRAM rewards.
+    // Items of an image: first the box items, then the class items (see the schedule note in the kernel; interleaving
+    // the two kinds in proportion measured 4 % slower).
     int l = 0;
     if (r < P.n_box) {
 #pragma unroll
@@ -352,25 +351,32 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, S
     int tg_cur = -1, tg_nxt = -1, tg_nn = -1;
     bool cur_loaded = false, nxt_loaded = false;
     unsigned phase_bits = 0u;                                        // bit s = parity the next wait on stage s uses
-    // Schedule: a CTA works on groups of kStreamWarps consecutive items (warp w takes the w-th), its k-th group being
-    // group perm(k * gridDim + cta).  perm is the identity in the shipped build: all SMs then sweep one contiguous window
-    // of rows, which is what the memory system rewards -- a multiplicative permutation of the groups (or of single items)
-    // balances the item kinds per SM better but measured 5-20 % slower.  The hook is kept for experiments (-DYS_STREAM_PERM).
-    const unsigned NG = P.n_groups16;
-    auto perm_next = [&](unsigned g) -> unsigned { g += P.perm_step; return g >= NG ? g - NG : g; };
-    const unsigned my_groups = blockIdx.x < NG ? (NG - 1u - blockIdx.x) / gridDim.x + 1u : 0u;
-    unsigned g_nn = (unsigned)(((unsigned long long)blockIdx.x * P.perm_mul) % NG);
+    // Schedule.  Round k covers the contiguous window of groups [k*G, (k+1)*G), G = gridDim.x, a group being kStreamWarps
+    // consecutive items (warp w takes the w-th): at any time all SMs sweep ONE contiguous window of rows, which is what
+    // DRAM rewards (scattering items or groups over the SMs measured 5-20 % slower).  Inside the window CTA c takes group
+    // (c + k*rotate) mod G.  Without the rotation a CTA's position relative to the image it is in moves by
+    // (G * kStreamWarps) mod items_per_img per round -- at the bench shape with 16 warps that is -2 items: a CTA would see
+    // only class items, or only background box items, for the whole kernel and the SMs finish 20 % apart.  The host
+    // picks `rotate` so that the per-round drift is ~0.38 of an image (golden-ratio sampling of the item kinds).
+    const unsigned G = gridDim.x;
+    const unsigned my_groups = P.rounds;
+    unsigned k_nn = 0u, rot_nn = blockIdx.x % G;      // round and rotated slot of the next group to decode
+    auto next_group_item = [&]() -> int {
+        const unsigned g = k_nn * G + rot_nn;
+        ++k_nn;
+        rot_nn += P.rotate;
+        if (rot_nn >= G) rot_nn -= G;
+        return g < P.n_groups16 ? (int)(g * kStreamWarps) + warp : P.total_items;      // past the end: padding item
+    };
     auto load_tg2 = [&](const Item &it) -> int { return it.n_live > 0 ? load_tg(it) : -1; };
     if (my_groups > 0u) {
-        cur = decode_item(L, P, (int)(g_nn * kStreamWarps) + warp);
-        g_nn = perm_next(g_nn);
+        cur = decode_item(L, P, next_group_item());
         tg_cur = load_tg2(cur);
         cur_loaded = cur.n_live > 0 && (cur.group >= 0 || __any_sync(0xffffffffu, tg_cur >= 0));
         if (cur_loaded) issue_item(L, P, M, cur, ring, smem_u32(&s_bar[warp][0]), lane);
     }
     if (my_groups > 1u) {
-        nxt = decode_item(L, P, (int)(g_nn * kStreamWarps) + warp);
-        g_nn = perm_next(g_nn);
+        nxt = decode_item(L, P, next_group_item());
         tg_nxt = load_tg2(nxt);
     }
     (void)item; (void)step;
@@ -385,8 +391,7 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, S
             if (nxt_loaded) issue_item(L, P, M, nxt, ring + (size_t)(s ^ 1) * kStageBytes, smem_u32(&s_bar[warp][s ^ 1]), lane);
             // and the assignment lookup of the one after it
             if (k + 2u < my_groups) {
-                nn = decode_item(L, P, (int)(g_nn * kStreamWarps) + warp);
-                g_nn = perm_next(g_nn);
+                nn = decode_item(L, P, next_group_item());
                 tg_nn = load_tg2(nn);
             }
         }
