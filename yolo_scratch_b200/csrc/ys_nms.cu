@@ -288,6 +288,217 @@ k_nms_suppress(const int *__restrict__ count, int A, const float4 *__restrict__ 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// k_nms_suppress_reg: the same greedy suppression with the COLUMNS resident in registers.
+// One block of 1024 threads per image; thread t owns the sorted boxes t, t+1024, ... (COLS of them): box, area, class
+// and an alive bit per column live in registers, so the N^2/2 pair tests read only the 64 kept-row boxes of the
+// current tile (shared-memory broadcasts) -- no shared-memory box table, no index indirection, no atomics.
+// Per 64-row tile: owners publish the tile -> diagonal 64x64 bitmask by warp ballots -> one thread resolves the tile
+// serially (greedy order) and compacts the kept rows -> every thread tests its later, alive columns against them.
+// Keep lists are identical to k_nms_suppress (the arithmetic of a pair test is the same function).
+// ---------------------------------------------------------------------------------------------------
+constexpr int kRegThreads = 1024;
+
+template <bool CLASS_AWARE, int COLS>
+__global__ void __launch_bounds__(kRegThreads, 1)
+k_nms_suppress_reg(const int *__restrict__ count, int A, const float4 *__restrict__ sbox, const float *__restrict__ sscore,
+                   const int *__restrict__ scls, const int *__restrict__ sanchor, float thr, float img_size,
+                   int *__restrict__ keep_anchor, float4 *__restrict__ keep_boxes, float *__restrict__ keep_scores,
+                   int *__restrict__ keep_labels, int *__restrict__ keep_count) {
+    __shared__ float4 s_tile[64];
+    __shared__ float s_tarea[64];
+    __shared__ int s_tcls[64];
+    __shared__ unsigned long long s_diag[64];
+    __shared__ float4 s_kbox[64];
+    __shared__ float s_karea[64];
+    __shared__ int s_kcls[64];
+    __shared__ unsigned s_talive[2];
+    __shared__ unsigned long long s_trem;
+    __shared__ int s_nk;
+    __shared__ unsigned s_alive[COLS * kRegThreads / 32];
+    const int b = blockIdx.x;
+    const int n = count[b];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (n == 0) {
+        if (tid == 0) keep_count[b] = 0;
+        return;
+    }
+    const float4 *gbox = sbox + (size_t)b * A;
+    const int *gcls = scls + (size_t)b * A;
+    float4 bx[COLS];
+    float ar[COLS];
+    int cl[COLS];
+    unsigned alive = 0u;
+    bool sane = true;      // finite, well-formed boxes: a pair that does not intersect then has IoU exactly 0
+#pragma unroll
+    for (int k = 0; k < COLS; ++k) {
+        const int c = k * kRegThreads + tid;
+        bx[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        cl[k] = -1;
+        if (c < n) {
+            bx[k] = gbox[c];
+            if (CLASS_AWARE) cl[k] = gcls[c];
+            alive |= 1u << k;
+        }
+        ar[k] = area_plain(bx[k]);
+        sane = sane && (ar[k] >= 0.f) && (fabsf(bx[k].x) + fabsf(bx[k].y) + fabsf(bx[k].z) + fabsf(bx[k].w) < 3.0e38f);
+    }
+    for (int i = tid; i < COLS * kRegThreads / 32; i += kRegThreads) s_alive[i] = 0u;
+    sane = __syncthreads_and(sane) && (0.f <= thr);
+
+    for (int t0 = 0; t0 < n; t0 += 64) {
+        const int tn = min(64, n - t0);
+        const int kt = t0 / kRegThreads, i_t = tid - (t0 - kt * kRegThreads);     // owners of the tile: 64 consecutive threads
+        if (i_t >= 0 && i_t < 64) {
+            float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
+            float ma = 0.f;
+            int mc = -1;
+            bool al = false;
+#pragma unroll
+            for (int k = 0; k < COLS; ++k)
+                if (k == kt) { mine = bx[k]; ma = ar[k]; mc = cl[k]; al = (alive >> k) & 1u; }
+            s_tile[i_t] = mine;
+            s_tarea[i_t] = ma;
+            if (CLASS_AWARE) s_tcls[i_t] = mc;
+            const unsigned m = __ballot_sync(0xffffffffu, al);      // the 64 owners are two whole warps (64 | 1024)
+            if (lane == 0) s_talive[i_t >> 5] = m;
+        }
+        __syncthreads();
+        // -- diagonal 64x64 bitmask tile by warp ballots: warp w handles rows w and w + 32
+        for (int r = warp; r < tn; r += kRegThreads / 32) {
+            const float4 bi = s_tile[r];
+            const float ai = s_tarea[r];
+            unsigned long long bits = 0ull;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int c = h * 32 + lane;
+                bool sup = false;
+                if (c > r && c < tn) {
+                    sup = suppresses(bi, ai, s_tile[c], thr);
+                    if (CLASS_AWARE) sup = sup && (s_tcls[c] == s_tcls[r]);
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, sup);
+                bits |= (unsigned long long)m << (32 * h);
+            }
+            if (lane == 0) s_diag[r] = bits;
+        }
+        __syncthreads();
+        // -- greedy resolution of the tile by ONE WARP: the 64 row masks live in registers (two per lane), the running
+        //    "removed" mask is replicated in every lane, one shuffle per row; then the lanes compact the kept rows for
+        //    the column pass (rows of zero extent -> NaN, padding to a multiple of 8 -> NaN: never a candidate)
+        if (warp == 0) {
+            const unsigned long long d0 = lane < tn ? s_diag[lane] : 0ull;
+            const unsigned long long d1 = lane + 32 < tn ? s_diag[lane + 32] : 0ull;
+            unsigned long long rem = ~((unsigned long long)s_talive[0] | ((unsigned long long)s_talive[1] << 32));
+            unsigned long long kept = 0ull;
+#pragma unroll
+            for (int r = 0; r < 64; ++r) {
+                const unsigned long long dr = __shfl_sync(0xffffffffu, r < 32 ? d0 : d1, r & 31);
+                if (!((rem >> r) & 1ull)) {      // uniform across the warp
+                    kept |= 1ull << r;
+                    rem |= dr;
+                }
+            }
+            const int nk = __popcll(kept);
+            const float qnan = __int_as_float(0x7fc00000);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int r = lane + 32 * h;
+                if ((kept >> r) & 1ull) {
+                    const int pos = __popcll(kept & ((1ull << r) - 1ull));
+                    float4 v = s_tile[r];
+                    if (sane && !(v.z > v.x && v.w > v.y)) v = make_float4(qnan, qnan, qnan, qnan);
+                    s_kbox[pos] = v;
+                    s_karea[pos] = s_tarea[r];
+                    if (CLASS_AWARE) s_kcls[pos] = s_tcls[r];
+                }
+            }
+            if (lane < ((nk + 7) & ~7) - nk) s_kbox[nk + lane] = make_float4(qnan, qnan, qnan, qnan);
+            if (lane == 0) { s_nk = nk; s_trem = rem; }
+        }
+        __syncthreads();
+        const int nk = s_nk;
+        if (i_t >= 0 && i_t < 64 && ((s_trem >> i_t) & 1ull)) alive &= ~(1u << kt);      // removed inside the tile
+        // -- kept rows of this tile suppress every later, still-alive column (registers vs shared-memory broadcasts)
+        if (nk > 0) {
+#pragma unroll
+            for (int k = 0; k < COLS; ++k) {
+                const int c = k * kRegThreads + tid;
+                if (!((alive >> k) & 1u) || c < t0 + 64) continue;
+                const float4 bj = bx[k];
+                const float aj = ar[k];
+                bool dead = false;
+                if (sane) {
+                    // Branch-free candidate pass: two boxes of positive extent intersect iff
+                    //   bi.z > bj.x && bj.z > bi.x && bi.w > bj.y && bj.w > bi.y
+                    // (min(a,b) - max(c,d) > 0 in fp32 <=> min(a,b) > max(c,d); the two remaining comparisons, each
+                    // box's own extent, are folded into the data: kept rows of zero extent were stored as NaN, and
+                    // a column of zero extent has ok_j false).  The exact IoU runs only on the candidates.
+                    if (bj.z > bj.x && bj.w > bj.y) {
+                        unsigned long long cand = 0ull;
+                        for (int q0 = 0; q0 < nk; q0 += 8) {          // s_kbox is padded with NaN rows to a multiple of 8
+                            unsigned m8 = 0u;
+#pragma unroll
+                            for (int u = 0; u < 8; ++u) {
+                                const float4 bi = s_kbox[q0 + u];
+                                const bool hit = bi.z > bj.x && bj.z > bi.x && bi.w > bj.y && bj.w > bi.y;
+                                m8 |= hit ? (1u << u) : 0u;
+                            }
+                            cand |= (unsigned long long)m8 << q0;
+                        }
+                        while (cand && !dead) {
+                            const int q = __ffsll((long long)cand) - 1;
+                            cand &= cand - 1ull;
+                            if (CLASS_AWARE && s_kcls[q] != cl[k]) continue;
+                            const float iou = iou_nms(s_kbox[q], s_karea[q], bj, aj);
+                            dead = !(iou <= thr);
+                        }
+                    }
+                } else {
+                    for (int q = 0; q < nk && !dead; ++q) {
+                        if (CLASS_AWARE && s_kcls[q] != cl[k]) continue;
+                        dead = suppresses(s_kbox[q], s_karea[q], bj, thr);
+                    }
+                }
+                if (dead) alive &= ~(1u << k);
+            }
+        }
+        // no barrier here: the next tile's first barrier orders these reads of s_k* before thread 0 rewrites them
+    }
+
+    // -- survivors: bitmap in sorted order, then one warp compacts (ballot prefix)
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < COLS; ++k)
+        if ((alive >> k) & 1u) atomicOr(&s_alive[(k * kRegThreads + tid) >> 5], 1u << (tid & 31));
+    __syncthreads();
+    if (warp == 0) {
+        int base = 0;
+        for (int c0 = 0; c0 < n; c0 += 32) {
+            const int c = c0 + lane;
+            const bool al = c < n && ((s_alive[c >> 5] >> (c & 31)) & 1u);
+            const unsigned m = __ballot_sync(0xffffffffu, al);
+            if (al) {
+                const size_t o = (size_t)b * A + base + __popc(m & ((1u << lane) - 1u));
+                const size_t s = (size_t)b * A + c;
+                if (keep_anchor) keep_anchor[o] = sanchor[s];
+                if (keep_boxes) {
+                    const float4 v = sbox[s];
+                    // boxes / img_size, clamp to [0,1]  (train_yolo11_cuda.py:347-350)
+                    float4 q = make_float4(YS_DIV(v.x, img_size), YS_DIV(v.y, img_size), YS_DIV(v.z, img_size), YS_DIV(v.w, img_size));
+                    q.x = fminf2(fmaxf2(q.x, 0.f), 1.f); q.y = fminf2(fmaxf2(q.y, 0.f), 1.f);
+                    q.z = fminf2(fmaxf2(q.z, 0.f), 1.f); q.w = fminf2(fmaxf2(q.w, 0.f), 1.f);
+                    keep_boxes[o] = q;
+                }
+                if (keep_scores) keep_scores[o] = sscore[s];
+                if (keep_labels) keep_labels[o] = scls[s];
+            }
+            base += __popc(m);
+        }
+        if (lane == 0) keep_count[b] = base;
+    }
+}
+
 struct NmsWorkspace {
     unsigned long long *keys;
     float4 *boxes, *sbox;
@@ -330,6 +541,18 @@ static int run_sort_suppress(const NmsWorkspace &W, int B, int A, float iou_thr,
     }
     k_nms_sort<<<B, kSortThreads, sort_smem, stream>>>(W.keys, W.count, A, boxes, cls, W.sbox, W.sscore, W.scls, W.sanchor);
     YS_CHECK_LAUNCH("k_nms_sort");
+    if (A <= 9 * kRegThreads) {      // register-resident columns (every 640 px / 8400-candidate case)
+#define YS_LAUNCH_REG(CA, COLS)                                                                                              \
+    k_nms_suppress_reg<CA, COLS><<<B, kRegThreads, 0, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr,      \
+                                                                img_size, keep_anchor, (float4 *)keep_boxes, keep_scores,     \
+                                                                keep_labels, keep_count)
+        if (A <= 2 * kRegThreads) { if (class_aware) YS_LAUNCH_REG(true, 2); else YS_LAUNCH_REG(false, 2); }
+        else if (A <= 5 * kRegThreads) { if (class_aware) YS_LAUNCH_REG(true, 5); else YS_LAUNCH_REG(false, 5); }
+        else { if (class_aware) YS_LAUNCH_REG(true, 9); else YS_LAUNCH_REG(false, 9); }
+#undef YS_LAUNCH_REG
+        YS_CHECK_LAUNCH("k_nms_suppress_reg");
+        return YS_OK;
+    }
     const int smem_boxes = A <= kSupSmemBoxes ? A : 0;
     const size_t sup_smem = suppress_smem_bytes(A, smem_boxes);
     if (class_aware)
