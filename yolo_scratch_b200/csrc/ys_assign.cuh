@@ -272,8 +272,16 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         }
     };
     __syncthreads();               // (fused) mbarrier initialised
-    if (ntiles > 0) stage_gt(0, min(kGtTile, n));            // overlaps the tile load of the fused path
-    __syncthreads();
+    // GT tile 0: one GT per thread goes into a register now and into shared memory after the decode below, so the
+    // latency of this (dependent) load hides under the decode instead of in front of a barrier
+    static_assert(kGtTile <= kScanThreads, "tile 0 is staged one GT per thread");
+    const int tn0 = ntiles > 0 ? min(kGtTile, n) : 0;
+    float4 q_pre = make_float4(0.f, 0.f, 0.f, 0.f);
+    bool v_pre = true;
+    if (tid < tn0) {
+        q_pre = io.gt_box[g0 + tid];
+        if (!FUSED) v_pre = io.gt_valid[g0 + tid] != 0.f;
+    }
 
     // ---- this anchor's predicted box (px) and centre (px)
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -317,6 +325,15 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         ax = c.x;
         ay = c.y;
     }
+    if (tid < tn0) {
+        S.box[tid] = q_pre;
+        S.area[tid] = area_eps_h(q_pre.x, q_pre.y, q_pre.z, q_pre.w);
+        S.any[tid] = 0;
+        S.own[tid] = 0;
+        S.rkey[tid] = 0ull;
+        S.valid[tid] = v_pre ? 1 : 0;
+    }
+    __syncthreads();
     const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
     // bounding box of this warp's anchor centres (non-live lanes neutral); order-preserving float <-> uint map so
     // that the dense entry point may be given any (also negative) anchor points

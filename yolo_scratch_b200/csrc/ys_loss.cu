@@ -880,7 +880,11 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     io.gt_off = W.gt_off; io.G = 0; io.gt_box = W.gt_box; io.gt_label_i = W.gt_label; io.gt_label_f = nullptr;
     io.gt_valid = nullptr; io.pd_box = nullptr; io.pd_scores = nullptr; io.anc = nullptr;
     io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags; io.forced = W.forced;
-    io.img_order = W.img_order; io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
+    io.img_order = W.img_order;
+#ifdef YS_NO_ORDER
+    io.img_order = nullptr;
+#endif
+    io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
     io.pbox = pred_boxes_px ? (float4 *)pred_boxes_px : W.pbox;
     io.tgi = target_gt_idx ? (int *)target_gt_idx : W.tgi;
     io.lab = W.lab;
