@@ -153,6 +153,21 @@ int ys_pairwise_iou(const float *boxes1, int N, const float *boxes2, int M, int 
 int ys_bbox_iou(const float *box1, const float *box2, int n, int xywh, int mode, float eps, float *out,
                 const float *gout, float *grad_box1, void *stream);
 
+/* ---------------------------------------------------------------------------
+ * Greedy detection-to-GT matching of evaluate_detections (utils/metrics.py:147-205, :211-256): per image,
+ * predictions in score-descending order, each takes the best-IoU unmatched GT (first maximum, class agnostic); true
+ * positive iff that IoU >= threshold (compared in double, as the reference does), and only then is the GT consumed.
+ *  pred_boxes (B, pred_stride, 4) xyxy, pred_scores (B, pred_stride) SORTED DESCENDING per image, pred_count (B) i32
+ *  (the layout ys_nms_batched writes); predictions with score < conf_thr are ignored (a suffix);
+ *  gt_boxes (N,4) + gt_off (B+1) i32: per-image CSR list, at most 1024 GT per image (max_gt = the largest count);
+ *  iou_thresholds_host: n_thresholds (<= 16) doubles on the HOST.
+ *  tp (B, pred_stride, n_thresholds) u8: 1 = true positive, for the first n_valid[b] predictions of image b.
+ */
+int ys_match_detections(const float *pred_boxes, const float *pred_scores, const int32_t *pred_count, int B,
+                        int pred_stride, const float *gt_boxes, const int32_t *gt_off, int max_gt, float conf_thr,
+                        const double *iou_thresholds_host, int n_thresholds, uint8_t *tp, int32_t *n_valid,
+                        void *stream);
+
 #ifdef __cplusplus
 }
 #endif

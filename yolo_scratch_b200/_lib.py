@@ -44,6 +44,8 @@ PROTOTYPES = {
     "ys_nms_single": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_float, c_void_p, c_void_p, c_void_p, c_size_t,
                               c_void_p]),
     "ys_pairwise_iou": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "ys_match_detections": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_float,
+                                    C.POINTER(C.c_double), c_int, c_void_p, c_void_p, c_void_p]),
     "ys_bbox_iou": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
 }
 

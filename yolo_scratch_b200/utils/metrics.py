@@ -30,3 +30,95 @@ def calculate_iou(box1, box2):
     if union <= 0:
         return 0.0
     return inter / union
+
+
+# ----------------------------------------------------------------------------------------------
+# mAP scoring: the matching loops run on the device, the AP arithmetic on the host
+# ----------------------------------------------------------------------------------------------
+def calculate_ap(tp, fp, n_gt):
+    """All-point-interpolated AP from the scores of the true and false positives (reference utils/metrics.py:277-323):
+    detections sorted by score (stable, true positives listed first), precision = tp/(tp+fp+1e-6), recall = tp/n_gt,
+    monotone precision envelope, sum of recall steps times precision."""
+    import numpy as np
+    if n_gt == 0:
+        return 0.0
+    dets = sorted([(float(s), 1) for s in tp] + [(float(s), 0) for s in fp], key=lambda d: d[0], reverse=True)
+    if not dets:
+        return 0.0
+    flags = np.array([d[1] for d in dets])
+    ctp, cfp = np.cumsum(flags), np.cumsum(1 - flags)
+    prec = ctp / (ctp + cfp + 1e-6)
+    rec = ctp / n_gt
+    mrec = np.concatenate([[0.0], rec, [1.0]])
+    mpre = np.concatenate([[0.0], prec, [0.0]])
+    for k in range(len(mpre) - 1, 0, -1):
+        mpre[k - 1] = np.maximum(mpre[k - 1], mpre[k])
+    idx = np.where(mrec[1:] != mrec[:-1])[0]
+    return np.sum((mrec[idx + 1] - mrec[idx]) * mpre[idx + 1])
+
+
+def match_detections(predictions, targets, conf_threshold, iou_thresholds):
+    """Device part of evaluate_detections: returns (tp_flags, scores, n_valid, n_gt) with tp_flags (B, P, T) uint8 on
+    the host, scores (B, P) fp32 on the host (score-descending per image), n_valid (B,), n_gt total."""
+    import ctypes as C
+    import numpy as np
+    B = len(predictions)
+    dev = None
+    for d in list(predictions) + list(targets):
+        if d["boxes"].is_cuda:
+            dev = d["boxes"].device
+            break
+    if dev is None:
+        raise _lib.YsError("evaluate_detections: the B200 path needs CUDA tensors (there is no CPU fallback)")
+    P = max(1, max(int(p["boxes"].shape[0]) for p in predictions))
+    pb = torch.zeros(B, P, 4, device=dev)
+    ps = torch.full((B, P), float("-inf"), device=dev)
+    pc = torch.zeros(B, dtype=torch.int32, device=dev)
+    for i, p in enumerate(predictions):
+        n = int(p["boxes"].shape[0])
+        if n:
+            pb[i, :n] = p["boxes"].to(dev, torch.float32)
+            ps[i, :n] = p["scores"].to(dev, torch.float32)
+            pc[i] = n
+    ps, order = torch.sort(ps, dim=1, descending=True, stable=True)            # :170 (scores are unique in practice)
+    pb = torch.gather(pb, 1, order.unsqueeze(-1).expand(-1, -1, 4)).contiguous()
+    counts = [int(t["boxes"].shape[0]) for t in targets]
+    off = torch.tensor([0] + list(np.cumsum(counts)), dtype=torch.int32, device=dev)
+    gt = (torch.cat([t["boxes"].to(dev, torch.float32).view(-1, 4) for t in targets], 0)
+          if sum(counts) else torch.zeros(1, 4, device=dev)).contiguous()
+    T = len(iou_thresholds)
+    thr = (C.c_double * T)(*[float(x) for x in iou_thresholds])
+    tp = torch.zeros(B, P, T, dtype=torch.uint8, device=dev)
+    nv = torch.zeros(B, dtype=torch.int32, device=dev)
+    check(_lib.lib().ys_match_detections(ptr(pb), ptr(ps.contiguous()), ptr(pc), B, P, ptr(gt), ptr(off), max(counts + [0]),
+                                         float(conf_threshold), thr, T, ptr(tp), ptr(nv), stream_ptr(dev)),
+          "ys_match_detections")
+    return tp.cpu().numpy(), ps.cpu().numpy(), nv.cpu().numpy(), int(sum(counts))
+
+
+def evaluate_detections(predictions, targets, conf_threshold=0.25, iou_threshold=0.5):
+    """Same signature and result dict as the reference (utils/metrics.py:84-274): precision and recall at IoU 0.5,
+    mAP50 = AP at the first threshold, mAP50-95 = mean AP over the threshold ladder."""
+    import numpy as np
+    if iou_threshold == 0.5:
+        ladder = np.arange(0.5, 0.95 + 1e-6, 0.05)                                                   # :134
+    else:
+        ladder = np.arange(iou_threshold, min(1.0, iou_threshold + 0.45) + 1e-6, 0.05)              # :137
+    thresholds = list(ladder) + [0.5]                      # the last column serves precision / recall (:252)
+    if len(predictions) == 0:
+        return {"precision": 0.0, "recall": 0.0, "mAP50": 0.0, "mAP50-95": 0.0 if len(ladder) == 0 else float(np.mean([0.0] * len(ladder)))}
+    tp, scores, nv, n_gt = match_detections(predictions, targets, conf_threshold, thresholds)
+    aps = []
+    for t in range(len(ladder)):
+        tps, fps = [], []
+        for b in range(tp.shape[0]):
+            s, f = scores[b, :nv[b]], tp[b, :nv[b], t].astype(bool)
+            tps.extend(s[f].tolist())
+            fps.extend(s[~f].tolist())
+        aps.append(calculate_ap(tps, fps, n_gt))
+    n_tp = int(sum(tp[b, :nv[b], -1].sum() for b in range(tp.shape[0])))
+    n_det = int(nv.sum())
+    precision = n_tp / n_det if n_det > 0 else 0.0
+    recall = n_tp / n_gt if n_gt > 0 else 0.0
+    return {"precision": precision, "recall": recall, "mAP50": aps[0] if aps else 0.0,
+            "mAP50-95": np.mean(aps) if aps else 0.0}
