@@ -168,6 +168,15 @@ int ys_match_detections(const float *pred_boxes, const float *pred_scores, const
                         const double *iou_thresholds_host, int n_thresholds, uint8_t *tp, int32_t *n_valid,
                         void *stream);
 
+/* ---------------------------------------------------------------------------
+ * cda_nms (utils/metrics.py:484-620 with _calcYmat :440-453 and _calc_dGA :456-481): greedy suppression by the
+ * Gaussian-angle distance between the ellipses inscribed in the boxes (fp64), at most max_det (<= 32) survivors.
+ *  boxes (B, stride, 4) xyxy SORTED by score descending per image, angles (B, stride) radians or NULL (= 0),
+ *  count (B) i32.  keep_idx (B, max_det) i32: positions in the sorted order; keep_count (B) i32.
+ */
+int ys_cda_nms(const float *boxes, const float *angles, const int32_t *count, int B, int stride, int max_det,
+               double dga_thresh, int32_t *keep_idx, int32_t *keep_count, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -72,3 +72,27 @@ np.savez_compressed(os.path.join(HERE, "calculate_ap_known.npz"),
                     fp=np.array([np.array(c[1] + [-1.0] * (64 - len(c[1]))) for c in cases]),
                     n_gt=np.array([c[2] for c in cases]), ap=np.array([c[3] for c in cases]))
 print([c[3] for c in cases])
+
+# ---- cda_nms: reference keep lists on clustered detections, with and without angles
+from utils.metrics import cda_nms      # noqa: E402  (reference)
+
+for seed, n, n_clusters, with_angles, max_det, thr in [(80, 200, 6, False, 10, 0.15), (81, 400, 25, True, 10, 0.15),
+                                                       (82, 60, 3, False, 5, 0.3), (83, 500, 40, True, 20, 0.05)]:
+    g = torch.Generator().manual_seed(seed)
+    cc = 0.15 + 0.7 * torch.rand(n_clusters, 2, generator=g)
+    cw = 0.04 + 0.12 * torch.rand(n_clusters, 2, generator=g)
+    k = torch.randint(0, n_clusters, (n,), generator=g)
+    c = cc[k] + 0.01 * torch.randn(n, 2, generator=g)
+    wh = cw[k] * (1 + 0.1 * torch.randn(n, 2, generator=g)).clamp(0.5, 1.5)
+    boxes = torch.cat((c - wh / 2, c + wh / 2), 1).clamp(0, 1)
+    scores = (torch.randperm(8192, generator=g)[:n].float() + 1) / 8193.0
+    pred = {"boxes": boxes, "scores": scores, "labels": k.clone()}
+    if with_angles:
+        pred["angles"] = (torch.rand(n, generator=g) - 0.5) * 3.0
+    out = cda_nms(pred, max_detections=max_det, dga_thresh=thr)
+    # identify the kept rows by their (unique) scores
+    kept = [int((scores == s).nonzero()[0, 0]) for s in out["scores"]]
+    np.savez_compressed(os.path.join(HERE, f"cda_nms_s{seed}.npz"), boxes=boxes.numpy(), scores=scores.numpy(),
+                        labels=k.numpy(), angles=pred.get("angles", torch.zeros(0)).numpy(), with_angles=with_angles,
+                        max_det=max_det, thr=thr, kept=np.array(kept), kept_boxes=out["boxes"].numpy())
+    print("cda_nms", seed, kept)

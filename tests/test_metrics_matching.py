@@ -78,3 +78,21 @@ def test_matching_properties_after_nms(cuda_lib):
         shuffled.append({k: v[perm] for k, v in d.items()})
     tp2, scores2, nv2, _ = match_detections(shuffled, tgts, 0.25, thr)
     assert np.array_equal(nv, nv2) and np.array_equal(tp, tp2) and np.array_equal(scores, scores2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", [80, 81, 82, 83])
+def test_cda_nms_golden(cuda_lib, seed):
+    """keep list of the reference's cda_nms (dGA-distance greedy NMS, top-k) on clustered detections."""
+    from yolo_scratch_b200.utils.metrics import cda_nms
+    g = np.load(os.path.join(GOLD, f"cda_nms_s{seed}.npz"))
+    pred = {"boxes": torch.tensor(g["boxes"]).cuda(), "scores": torch.tensor(g["scores"]).cuda(),
+            "labels": torch.tensor(g["labels"]).cuda()}
+    if bool(g["with_angles"]):
+        pred["angles"] = torch.tensor(g["angles"]).cuda()
+    out = cda_nms(pred, max_detections=int(g["max_det"]), dga_thresh=float(g["thr"]))
+    kept = [int((pred["scores"] == s).nonzero()[0, 0]) for s in out["scores"]]
+    assert kept == g["kept"].tolist()
+    assert torch.equal(out["boxes"].cpu(), torch.tensor(g["kept_boxes"]))
+    assert torch.equal(out["labels"].cpu(), torch.tensor(g["labels"])[g["kept"]])
+    assert set(out.keys()) == {"boxes", "scores", "angles", "labels"}

@@ -46,6 +46,7 @@ PROTOTYPES = {
     "ys_pairwise_iou": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "ys_match_detections": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_float,
                                     C.POINTER(C.c_double), c_int, c_void_p, c_void_p, c_void_p]),
+    "ys_cda_nms": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, C.c_double, c_void_p, c_void_p, c_void_p]),
     "ys_bbox_iou": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
 }
 

@@ -99,3 +99,92 @@ extern "C" int ys_match_detections(const float *pred_boxes, const float *pred_sc
     YS_CHECK_LAUNCH("k_match");
     return YS_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// cda_nms: greedy suppression with the Gaussian-angle distance dGA between the ellipses inscribed in
+// the boxes, at most max_det survivors (reference utils/metrics.py:440-620: _calcYmat, _calc_dGA, cda_nms).
+// Candidates arrive score-descending; a candidate is dropped iff dGA(candidate, kept) < dga_thresh for some kept one.
+// fp64 like the reference (numpy).  One warp per image: lane k holds kept detection k (max_det <= 32), the candidates
+// are walked in order until max_det are kept.  Parity with numpy's LAPACK-based det/inv is at tolerance level
+// (closed-form 2x2 determinant and inverse here), which only matters for a pair sitting exactly on the threshold.
+// ---------------------------------------------------------------------------------------------------
+namespace ys {
+
+struct Ellipse {
+    double y11, y12, y21, y22, det, xc, yc;
+};
+
+__device__ __forceinline__ Ellipse ellipse_of(float4 bx, float phi_f) {
+    // fp32 box arithmetic exactly as the torch code (:555-566), then double
+    const float w = bx.z - bx.x, h = bx.w - bx.y;
+    const float hw = w / 2.0f, hh = h / 2.0f;
+    const double a = (double)fmaxf(hw, hh), b = (double)fminf(hw, hh);
+    Ellipse e;
+    e.xc = (double)((bx.x + bx.z) / 2.0f);
+    e.yc = (double)((bx.y + bx.w) / 2.0f);
+    const double phi = (double)phi_f;
+    const double c = cos(phi), s = sin(phi);
+    const double ia = 1.0 / (a * a), ib = 1.0 / (b * b);
+    // (R diag(ia, ib)) R^T, products in the reference's association order (:451-454)
+    const double m11 = c * ia, m12 = -s * ib, m21 = s * ia, m22 = c * ib;
+    e.y11 = m11 * c + m12 * -s;
+    e.y12 = m11 * s + m12 * c;
+    e.y21 = m21 * c + m22 * -s;
+    e.y22 = m21 * s + m22 * c;
+    e.det = e.y11 * e.y22 - e.y12 * e.y21;
+    return e;
+}
+
+__device__ __forceinline__ double dga_of(const Ellipse &i, const Ellipse &j) {
+    const double kHalfPi = 1.5707963267948966;
+    const double s11 = i.y11 + j.y11, s12 = i.y12 + j.y12, s21 = i.y21 + j.y21, s22 = i.y22 + j.y22;
+    const double det_s = s11 * s22 - s12 * s21;
+    if (det_s <= 0.0 || i.det <= 0.0 || j.det <= 0.0) return kHalfPi;                 // :470
+    const double mult = 4.0 * sqrt(i.det * j.det) / det_s;
+    const double dx = i.xc - j.xc, dy = i.yc - j.yc;
+    // v = Yj d ; u = inv(Ysum) v ; t = Yi u ; e = -0.5 d.t   (:478)
+    const double v1 = j.y11 * dx + j.y12 * dy, v2 = j.y21 * dx + j.y22 * dy;
+    const double u1 = (s22 * v1 - s12 * v2) / det_s, u2 = (-s21 * v1 + s11 * v2) / det_s;
+    const double t1 = i.y11 * u1 + i.y12 * u2, t2 = i.y21 * u1 + i.y22 * u2;
+    const double ex = -0.5 * (dx * t1 + dy * t2);
+    double ct = mult * exp(ex);
+    ct = ct > 1.0 ? 1.0 : (ct < -1.0 ? -1.0 : ct);
+    return acos(ct);
+}
+
+__global__ void __launch_bounds__(128)
+k_cda_nms(const float4 *__restrict__ boxes, const float *__restrict__ angles, const int *__restrict__ count, int B,
+          int stride, int max_det, double thr, int *__restrict__ keep_idx, int *__restrict__ keep_count) {
+    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (b >= B) return;
+    const int n = count[b];
+    const float4 *bx = boxes + (size_t)b * stride;
+    const float *an = angles ? angles + (size_t)b * stride : nullptr;
+    Ellipse mine = {};       // lane k: kept detection k
+    int nk = 0;
+    for (int c = 0; c < n && nk < max_det; ++c) {
+        const Ellipse cand = ellipse_of(bx[c], an ? an[c] : 0.f);
+        const bool dup = lane < nk && dga_of(cand, mine) < thr;
+        if (!__any_sync(0xffffffffu, dup)) {
+            if (lane == nk) mine = cand;
+            if (lane == 0) keep_idx[(size_t)b * max_det + nk] = c;
+            ++nk;
+        }
+    }
+    if (lane == 0) keep_count[b] = nk;
+}
+
+}  // namespace ys
+
+extern "C" int ys_cda_nms(const float *boxes, const float *angles, const int32_t *count, int B, int stride, int max_det,
+                          double dga_thresh, int32_t *keep_idx, int32_t *keep_count, void *stream_v) {
+    YS_REQUIRE(B >= 1 && stride >= 1, YS_ERR_BAD_ARG, "B and stride must be >= 1");
+    YS_REQUIRE(boxes && count && keep_idx && keep_count, YS_ERR_BAD_ARG, "null pointer");
+    YS_REQUIRE(max_det >= 1 && max_det <= 32, YS_ERR_UNSUPPORTED, "max_det must be in [1, 32]");
+    YS_REQUIRE(((uintptr_t)boxes & 15) == 0, YS_ERR_BAD_ARG, "boxes must be 16-byte aligned");
+    k_cda_nms<<<(B + 3) / 4, 128, 0, (cudaStream_t)stream_v>>>((const float4 *)boxes, angles, count, B, stride, max_det,
+                                                               dga_thresh, keep_idx, keep_count);
+    YS_CHECK_LAUNCH("k_cda_nms");
+    return YS_OK;
+}

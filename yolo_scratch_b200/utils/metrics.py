@@ -122,3 +122,34 @@ def evaluate_detections(predictions, targets, conf_threshold=0.25, iou_threshold
     recall = n_tp / n_gt if n_gt > 0 else 0.0
     return {"precision": precision, "recall": recall, "mAP50": aps[0] if aps else 0.0,
             "mAP50-95": np.mean(aps) if aps else 0.0}
+
+
+def cda_nms(predictions, max_detections=10, dga_thresh=0.15):
+    """Same signature and result dict as the reference (utils/metrics.py:484-620): greedy suppression with the
+    Gaussian-angle distance of the inscribed ellipses, top `max_detections` kept; keys boxes / scores / angles
+    (+ labels when given), in score-descending order."""
+    boxes, scores = predictions["boxes"], predictions["scores"]
+    angles = predictions.get("angles", None)
+    labels = predictions.get("labels", None)
+    if len(boxes) == 0:
+        out = {"boxes": boxes, "scores": scores, "angles": angles if angles is not None else torch.zeros(0, device=boxes.device)}
+        if labels is not None:
+            out["labels"] = labels
+        return out
+    _lib.require_cuda(boxes, "predictions['boxes']")
+    dev = boxes.device
+    order = torch.argsort(scores, descending=True, stable=True)                     # :569 (scores unique in practice)
+    sb = boxes.detach().float()[order].contiguous().view(1, -1, 4)
+    sa = angles.detach().float()[order].contiguous().view(1, -1) if angles is not None else None
+    n = sb.shape[1]
+    cnt = torch.tensor([n], dtype=torch.int32, device=dev)
+    keep = torch.zeros(1, max_detections, dtype=torch.int32, device=dev)
+    kc = torch.zeros(1, dtype=torch.int32, device=dev)
+    check(_lib.lib().ys_cda_nms(ptr(sb), ptr(sa) if sa is not None else None, ptr(cnt), 1, n, int(max_detections),
+                                float(dga_thresh), ptr(keep), ptr(kc), stream_ptr(dev)), "ys_cda_nms")
+    kept = order[keep[0, :int(kc.item())].long()]
+    out = {"boxes": boxes[kept], "scores": scores[kept],
+           "angles": angles[kept] if angles is not None else torch.zeros(len(kept), device=dev)}
+    if labels is not None:
+        out["labels"] = labels[kept]
+    return out
