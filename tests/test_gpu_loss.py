@@ -83,6 +83,10 @@ def test_loss_vs_oracle_640_with_spliced_assignment(cuda_lib, seed, B, max_gt, k
     # same GT density on a small image: almost every GT is at risk or forced
     (211, 2, 320, {"fixed_count": 300, "dense": True, "p_tiny": 0.1, "p_nested": 0.2}),
     (212, 2, 320, {"fixed_count": 70, "p_tiny": 0.2, "p_nested": 0.3}),     # just above the containment-hint limit (64)
+    # more than 1024 GT in the batch: the general k_pack_gt (not the one-GT-per-thread fast path) packs them
+    (213, 8, 320, {"fixed_count": 300, "dense": True, "p_tiny": 0.05, "p_nested": 0.1}),
+    # more GT in ONE image than the fix-up's shared-memory scratch holds (1536): global-scratch fix-up, 7 GT tiles
+    (214, 1, 320, {"fixed_count": 1700, "dense": True, "p_tiny": 0.02, "p_nested": 0.05}),
 ])
 def test_loss_dense_scene_vs_oracle(cuda_lib, seed, B, imgsz, kw):
     spliced_case(seed, B, imgsz, kw.get("fixed_count", 20), kw)
@@ -201,3 +205,29 @@ def test_loss_full_config2_properties(cuda_lib):
         assert torch.equal(c2.last_export["target_gt_idx"], ex["target_gt_idx"][16 * s:16 * (s + 1)])
         acc += it.double().cpu() * tss_s
     assert torch.allclose(acc / tss, items.double().cpu(), rtol=1e-5)
+
+
+def test_general_pack_unsorted_many_gt(cuda_lib):
+    """More than 1024 GT with interleaved batch_idx: the general k_pack_gt's stable-rank walk.  Within-image order is
+    kept, so the result must equal the sorted call's bit for bit (same kernels, same inputs after packing); rows with
+    batch_idx outside [0, B) are dropped."""
+    B = 6
+    feats = synth.make_head_levels(B, 320, 80, 16, seed=240)
+    batch = synth.make_gt_batch(B, 80, 260, seed=241, imgsz=320, fixed_count=260, dense=True)
+    assert batch["cls"].shape[0] > 1024
+    total, items, grads, _ = run_cuda(feats, batch, 80)
+    per_img = [list(torch.nonzero(batch["batch_idx"] == b).flatten().tolist()) for b in range(B)]
+    perm = []
+    while any(per_img):
+        for lst in per_img:
+            if lst:
+                perm.append(lst.pop(0))
+    perm = torch.tensor(perm)
+    sh = {k: v[perm] for k, v in batch.items()}
+    sh = {"batch_idx": torch.cat((sh["batch_idx"], torch.tensor([B, -3]))),
+          "cls": torch.cat((sh["cls"], torch.zeros(2, 1, dtype=torch.long))),
+          "bboxes": torch.cat((sh["bboxes"], torch.rand(2, 4)))}
+    total2, items2, grads2, _ = run_cuda(feats, sh, 80)
+    assert torch.equal(items, items2) and torch.equal(total, total2)
+    for a, b in zip(grads, grads2):
+        assert torch.equal(a, b)
