@@ -186,6 +186,54 @@ __device__ __forceinline__ int resolve_row(const AssignIO &io, const LevelSet &L
     return g;
 }
 
+// The same row resolve (loops 1 and 2 included) by a group of W lanes (W a power of two, 1..32; groups are aligned
+// lane ranges of a warp, every lane of the warp calls this).  The final resolve picks W from the number of rows it
+// has to redo: few rows -> a warp each, hundreds (dense scenes) -> a thread each, so the GT loop is never the
+// serial part.  Overlaps go through the lazy form (no division for disjoint boxes, same bits).
+template <bool FUSED>
+__device__ __forceinline__ int resolve_row_group(const AssignIO &io, const LevelSet &L, int b, int k, int g0, int n,
+                                                 const int *forced, int W, bool active, float &ov_out) {
+    const int sub = threadIdx.x & (W - 1);
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+    float ax = 0.f, ay = 0.f, area_p = 0.f;
+    int cnt = 0;
+    unsigned first = 0xFFFFFFFFu;
+    unsigned long long best = 0ull;
+    if (active) {
+        p = FUSED ? __ldcg(io.pbox + (size_t)b * L.A + k) : io.pd_box[(size_t)b * L.A + k];
+        anchor_centre<FUSED>(io, L, k, ax, ay);
+        area_p = area_eps_h(p.x, p.y, p.z, p.w);
+        float best_ov = -1.f;      // this lane's first maximum (ascending j)
+        int best_j = 0;
+#pragma unroll 4
+        for (int j = sub; j < n; j += W) {
+            const float4 q = io.gt_box[g0 + j];
+            const float ov = iou_assign_lazy(p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
+            const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
+            const bool m = (centre_in_box(ax, ay, q) && valid) || forced[2 * j] == k || forced[2 * j + 1] == k;
+            if (m) { ++cnt; first = min(first, (unsigned)j); }
+            if (ov > best_ov) { best_ov = ov; best_j = j; }
+        }
+        if (best_ov >= 0.f) best = argmax_key(best_ov, (unsigned)best_j);
+    }
+    for (int o = W >> 1; o > 0; o >>= 1) {
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+        best = other > best ? other : best;
+    }
+    int g = -1;
+    if (cnt > 1) g = (int)argmax_key_index(best);
+    else if (cnt == 1) g = (int)first;
+    float ov = 0.f;
+    if (active && g >= 0) {
+        const float4 q = io.gt_box[g0 + g];
+        ov = iou_assign(p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
+    }
+    ov_out = ov;
+    return g;
+}
+
 // Shared-memory layout: the scan phase and the fix-up phase never overlap in time, so they alias one buffer.
 struct ScanSmem {
     float4 box[kGtTile];
@@ -229,6 +277,12 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         // for k_pack_gt (whose outputs -- image order, GT lists -- are read from the next line on)
         cudaTriggerProgrammaticLaunchCompletion();
         cudaGridDependencySynchronize();
+#ifdef YS_FIXTIME
+        if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+            unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+            printf("START t=%llu\n", t_);
+        }
+#endif
     }
     const int b = (FUSED && io.img_order) ? io.img_order[blockIdx.y] : (int)blockIdx.y;
     // fused: blocks are cut per level (a block never straddles two levels: one tensor operation loads its tile)
@@ -551,9 +605,17 @@ __device__ __forceinline__ void fix_argmax(const LevelSet &L, const AssignIO &io
     }
 }
 
+#ifdef YS_FIXTIME         // timing experiment: thread 0 of every fix-up prints its phase stamps (ns) once it is done
+#define YS_STAMP(i) do { if (threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); stamp[i] = t_; } } while (0)
+#else
+#define YS_STAMP(i) do { } while (0)
+#endif
+#ifndef YS_FIXDIAG
+#define YS_FIXDIAG 0      // timing experiments only: bit0 skip phase 1, bit1 skip loop 2, bit2 skip phase 3 (results wrong)
+#endif
 template <bool FUSED>
 __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, void *scratch, int cap, int nblk) {
-    __shared__ int s_nneedy, s_ncmp, s_nlost, s_resume, s_nfired, s_want;
+    __shared__ int s_nneedy, s_ncmp, s_nlost, s_resume, s_nfired, s_want, s_nuniq, s_nlonely;
     __shared__ double s_delta[kScanThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kScanThreads / 32;
@@ -575,7 +637,11 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
     int *lost = in_smem ? s_int + 6 * cap : (gs + 5 * (size_t)n);
     unsigned long long *keyp = in_smem ? s_key : (io.best_key + g0);
 
-    if (tid == 0) { s_nneedy = 0; s_ncmp = 0; s_nlost = 0; }
+#ifdef YS_FIXTIME
+    unsigned long long stamp[8] = {};
+#endif
+    YS_STAMP(0);
+    if (tid == 0) { s_nneedy = 0; s_ncmp = 0; s_nlost = 0; s_nuniq = 0; s_nlonely = 0; s_nfired = 0; }
     if (tid < kWarps) s_delta[tid] = 0.0;
     __syncthreads();
     // ---- A: which GT need a forced assignment?  (common case: none)
@@ -586,6 +652,7 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
         if (in_smem) cntp[j] = c;
         const bool lonely1 = valid && fl == 0;           // loop 1 (:117-139): valid GT with no anchor centre inside
         forced[2 * j] = lonely1 ? -2 : -1;               // -2: pending, resolved below
+        if (lonely1) atomicAdd(&s_nlonely, 1);
         forced[2 * j + 1] = -1;
         // risk GT: the scan already found the arg-max anchor (all blocks of the image are done: key is final)
         const bool have = FUSED;      // fused: the scan left every GT's arg-max key in best_key (all blocks are done)
@@ -599,6 +666,7 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
     }
     __syncthreads();
     const int nneedy = s_nneedy;
+    YS_STAMP(1);
     if (nneedy > 0) {      // block-uniform
         // ---- B: arg-max over all anchors of IoU(anchor, GT j), first maximum (:136, :156), for the needy GT
         //      the scan did not cover
@@ -613,6 +681,7 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
         __syncthreads();
         // ---- 1: first resolve (:142) for the anchors loop 1 touched; everyone else keeps the scan's result
         for (int q = warp; q < nneedy; q += kWarps) {
+            if (YS_FIXDIAG & 1) break;
             const int j = needy[q];
             const int k = forced[2 * j];
             if (k < 0) continue;
@@ -629,6 +698,7 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
             }
         }
         __syncthreads();
+        YS_STAMP(2);
         // ---- B': GT that own nothing now but were not on the needy list (they lost their only anchor in phase 1)
         for (int j = tid; j < n; j += kScanThreads) {
             const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
@@ -645,32 +715,50 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
         // owner of every candidate anchor after phase 1
         for (int j = tid; j < n; j += kScanThreads) tg0[j] = kk[j] >= 0 ? tgi[kk[j]] : -1;
         __syncthreads();
-        // ---- 2: loop 2 (:146-162): sequential in g; later GT see the edits of earlier ones.  A GT whose only
-        //      anchor is stolen inside this loop has no arg-max yet: the serial thread stops there, the block
-        //      computes it, and the loop resumes at the same GT.
-        if (tid == 0) { s_resume = 0; s_nfired = 0; }
+        // ---- 2: loop 2 (:146-162): sequential in g; later GT see the edits of earlier ones.  Warp 0 walks the GT
+        //      32 at a time (ballot over "owns nothing"), handles the first such GT and looks again from the next
+        //      one on, because the anchor it just took may have been the only one of a later GT.  The GT that
+        //      fired and their anchors are listed in lost[] / needy[] (needy[] is free after phase 1): "who owns
+        //      anchor k now" = the latest listed thief of k, else the owner after phase 1.
+        //      Dense path only: a GT whose only anchor is stolen inside this loop has no arg-max yet -- the walk
+        //      stops there, the block computes it, and the walk resumes at the same GT.
+        YS_STAMP(3);
+        int *thief_k = needy;
+        if (tid == 0) { s_resume = 0; s_nfired = 0; s_want = -1; }
         __syncthreads();
         while (true) {
-            if (tid == 0) {
-                int nfired = s_nfired, want = -1;               // fired GT are remembered in lost[] (reused)
-                for (int j = s_resume; j < n; ++j) {
-                    const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
-                    if (!valid || cntp[j] != 0) continue;
-                    const int k = kk[j];
-                    if (k < 0) { want = j; s_resume = j; break; }
-                    int gold = tg0[j];
-                    for (int f = 0; f < nfired; ++f)
-                        if (kk[lost[f]] == k) gold = lost[f];   // stolen earlier in this loop: latest thief owns it
-                    if (gold >= 0) cntp[gold] -= 1;
-                    cntp[j] += 1;
-                    forced[2 * j + 1] = k;
-                    lost[nfired++] = j;
+            if (warp == 0 && !(YS_FIXDIAG & 2)) {
+                int nf = s_nfired, want = -1, c = s_resume;
+                while (c < n) {
+                    const int jj = c + lane;
+                    const bool z = jj < n && cntp[jj] == 0 && (FUSED || io.gt_valid[g0 + jj] != 0.f);
+                    const unsigned m = __ballot_sync(0xffffffffu, z);
+                    if (m == 0u) { c += 32; continue; }
+                    const int jf = c + __ffs(m) - 1;
+                    const int k = kk[jf];
+                    if (k < 0) { want = jf; break; }
+                    int latest = -1;
+                    for (int f0 = 0; f0 < nf; f0 += 32) {
+                        const int f = f0 + lane;
+                        const unsigned hm = __ballot_sync(0xffffffffu, f < nf && thief_k[f] == k);
+                        if (hm) latest = f0 + 31 - __clz(hm);
+                    }
+                    if (lane == 0) {
+                        const int gold = latest >= 0 ? lost[latest] : tg0[jf];
+                        if (gold >= 0) cntp[gold] -= 1;
+                        cntp[jf] += 1;
+                        forced[2 * jf + 1] = k;
+                        lost[nf] = jf;
+                        thief_k[nf] = k;
+                    }
+                    ++nf;
+                    __syncwarp();
+                    c = jf + 1;
                 }
-                s_nfired = nfired;
-                s_want = want;
+                if (lane == 0) { s_nfired = nf; s_want = want; s_resume = want >= 0 ? want : n; }
             }
             __syncthreads();
-            if (s_want < 0) break;                              // block-uniform
+            if (FUSED || s_want < 0) break;                     // block-uniform
             fix_argmax<FUSED>(L, io, b, g0, &s_want, 1, keyp);
             __syncthreads();
             if (tid == 0) {
@@ -680,17 +768,55 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
             }
             __syncthreads();
         }
-        // ---- 3: final resolve (:165) from mask_pos alone, for every anchor that carries a forced entry
+        // ---- 3: final resolve (:165) from mask_pos alone, for every anchor that carries a forced entry.
+        //      3a  the anchors to redo, listed in a fixed order: loop 1's in GT order (ballot compaction by warp 0),
+        //          then loop 2's in firing order (they are thief_k[] already).  A fixed order keeps the fp64 sum
+        //          of the target-score corrections the same every run.
+        //      3b  one owner per distinct anchor: the first row of the list naming it
+        //      3c  rows resolved by groups of W lanes, W from the row count; the group's first lane finishes
+        //          the row (label, score, norm), so those global round trips overlap across the block
+        YS_STAMP(4);
+        const int nf = (YS_FIXDIAG & 4) ? 0 : s_nfired;
+        int *row_all = tg0;          // [n1 + nf] <= 2n ints: tg0[] + lost[] (the thief list is not needed as GT any more)
+        int *row_k = needy;          // [n1 + nf] ints: needy[] + kk[]; -1 = a duplicate of an earlier row
+        if (warp == 0) {
+            int base = 0;
+            if (s_nlonely > 0 && !(YS_FIXDIAG & 4)) {
+                for (int c = 0; c < n; c += 32) {
+                    const int jj = c + lane;
+                    const int k = jj < n ? forced[2 * jj] : -1;
+                    const unsigned m = __ballot_sync(0xffffffffu, k >= 0);
+                    if (k >= 0) row_all[base + __popc(m & ((1u << lane) - 1u))] = k;
+                    base += __popc(m);
+                }
+            }
+            if (lane == 0) s_nuniq = base;
+        }
+        __syncthreads();
+        const int n1 = s_nuniq;
+        const int nrow = n1 + nf;
+        for (int f = tid; f < nf; f += kScanThreads) row_all[n1 + f] = thief_k[f];      // needy[] -> tg0[]/lost[]: disjoint
+        __syncthreads();
+        for (int q = tid; q < nrow; q += kScanThreads) {
+            const int k = row_all[q];
+            bool dup = false;
+#pragma unroll 4
+            for (int q2 = 0; q2 < q; ++q2) dup |= (row_all[q2] == k);
+            row_k[q] = dup ? -1 : k;
+        }
+        __syncthreads();
+        YS_STAMP(5);
+        int W = 32;
+        while (W > 1 && nrow * W > kScanThreads) W >>= 1;
+        const int groups = kScanThreads / W;
         double delta = 0.0;
-        for (int e = warp; e < 2 * n; e += kWarps) {
-            const int k = forced[e];
-            if (k < 0) continue;
-            bool seen = false;
-            for (int jj = lane; jj < e; jj += 32) seen |= (forced[jj] == k);
-            if (__any_sync(0xffffffffu, seen)) continue;
+        for (int q0 = 0; q0 < nrow; q0 += groups) {
+            const int q = q0 + tid / W;
+            const int k = q < nrow ? row_k[q] : -1;
+            const bool active = k >= 0;
             float ov;
-            const int gfin = resolve_row<FUSED>(io, L, b, k, g0, n, forced, true, ov);
-            if (lane == 0) {
+            const int gfin = resolve_row_group<FUSED>(io, L, b, k, g0, n, forced, W, active, ov);
+            if (active && (tid & (W - 1)) == 0) {
                 tgi[k] = gfin;
                 float nrm = 0.f;
                 int lb = -1;
@@ -704,9 +830,17 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
                 if (labp) labp[k] = lb;
             }
         }
+        delta = warp_sum(delta);
+        YS_STAMP(6);
         if (lane == 0) s_delta[warp] = delta;
     }
     __syncthreads();
+#ifdef YS_FIXTIME
+    if (tid == 0)
+        printf("FIX b=%d y=%d n=%d needy=%d uniq=%d t0=%llu A=%llu p1=%llu Bp=%llu l2=%llu fl=%llu p3=%llu\n", b, (int)blockIdx.y, n,
+               nneedy, s_nuniq + s_nfired, stamp[0], stamp[1] - stamp[0], stamp[2] - stamp[1], stamp[3] - stamp[2], stamp[4] - stamp[3],
+               stamp[5] - stamp[4], stamp[6] - stamp[5]);
+#endif
     // ---- leave the per-GT scratch zeroed for the next call
     for (int j = tid; j < n; j += kScanThreads) {
         io.owned_cnt[g0 + j] = 0;
