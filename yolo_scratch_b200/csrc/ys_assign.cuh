@@ -26,14 +26,21 @@ namespace ys {
 #define YS_SCAN_MINBLOCKS 4
 #endif
 constexpr int kScanThreads = YS_SCAN_THREADS;
-constexpr int kGtTile = 256;        // GT boxes staged per shared-memory tile
+constexpr int kGtTile = kScanThreads < 256 ? kScanThreads : 256;        // GT boxes staged per shared-memory tile
 constexpr int kFixSmemGt = 256;     // per-image GT count the fix-up handles with shared-memory scratch (dense entry point)
-constexpr int kFixSmemGtFused = 1536;   // same, fused path: the fix-up scratch lives in the (consumed) 64 KB TMA tile
+#ifndef YS_SCAN_STAGES
+#define YS_SCAN_STAGES 2
+#endif
+constexpr int kScanStages = YS_SCAN_STAGES;       // fused path: per-warp ring of side tiles (16 DFL bins x 32 anchors, 2 KB each)
+constexpr int kScanSideBytes = 16 * 32 * 4;
+constexpr int kScanTileBytes = (kScanThreads / 32) * kScanStages * kScanSideBytes;   // all warps' rings: 32 KB
+constexpr int kFixSmemGtFused = (kScanTileBytes / 36) & ~63;   // per-image GT count of the fused fix-up's shared-memory
+                                                               // scratch: it lives in the (consumed) rings, 36 B per GT
 constexpr float kDflReach = 15.5f;  // a decoded side is an expectation over bins 0..15: a predicted box reaches at most
                                     // 15 cells from its anchor centre (0.5 cell of slack for the approximate softmax)
-constexpr int kScanTileBytes = 64 * kScanThreads * 4;   // fused path: 64 box channels x 256 anchors, one TMA operation
 
-// Fused path: one 2-D tensor map per level over [B*C rows][h*w columns] fp32, box {kScanThreads columns, 64 rows}.
+// Fused path: one 2-D tensor map per level over [B*C rows][h*w columns] fp32, box {32 columns, 16 rows}: one side
+// (16 DFL bins) of one warp's 32 anchors per TMA operation.
 struct ScanMaps {
     CUtensorMap lvl[YS_MAX_LEVELS];
 };
@@ -55,6 +62,7 @@ struct AssignIO {
     int *owned_cnt;
     int *gt_flags;              // 1: some anchor centre lies inside
     const int *img_order;       // fused only (else nullptr): blockIdx.y -> image, a scheduling hint from k_pack_gt
+    int n_identity;             // fused only: the first n_identity launch slots are the images 0..n_identity-1 (see k_assign)
     int skip_fixup;             // profiling only
     unsigned long long *best_key;   // per-GT arg-max key over all anchors: written by the scan for risk GT (zero on
                                     // entry), by the fix-up for the others when an image has more than kFixSmemGt GT
@@ -260,23 +268,45 @@ union AssignSmem {
 template <bool FUSED>
 __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B, void *scratch, int cap, int nblk);
 
+// One side tile (16 DFL bins x the warp's 32 anchors) into stage `st` of the warp's ring; the stage's mbarrier gets the bytes.
+__device__ __forceinline__ void scan_issue_side(unsigned char *s_dyn, unsigned long long *mbar, const CUtensorMap *map, int warp,
+                                                int st, int side, int i0, int row0) {
+    const unsigned bar = (unsigned)__cvta_generic_to_shared(mbar);
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(s_dyn + (size_t)(warp * kScanStages + st) * kScanSideBytes);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kScanSideBytes) : "memory");
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(i0 + 32 * warp), "r"(row0 + 16 * side), "r"(bar) : "memory");
+}
+
+#ifdef YS_SCANTIME        // timing experiment: thread 0 of a sample of blocks prints the block's phase stamps (ns)
+#define YS_BSTAMP(i) do { if (threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); bst[i] = t_; } } while (0)
+#else
+#define YS_BSTAMP(i) do { } while (0)
+#endif
 template <bool FUSED>
 __global__ void __launch_bounds__(kScanThreads, YS_SCAN_MINBLOCKS)
 k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
-    // dynamic shared memory: [fused: 64 x 256 fp32 tile of the block's box channels][AssignSmem]
+    // dynamic shared memory: [fused: per-warp rings of side tiles, kScanStages x 2 KB each][AssignSmem]
     extern __shared__ __align__(128) unsigned char s_dyn[];
     AssignSmem &sm = *reinterpret_cast<AssignSmem *>(s_dyn + (FUSED ? kScanTileBytes : 0));
-    __shared__ __align__(8) unsigned long long s_mbar;
+    __shared__ __align__(8) unsigned long long s_mbar[kScanThreads / 32][kScanStages];
     __shared__ float s_red[kScanThreads / 32];
     __shared__ int s_flag;
     ScanSmem &S = sm.s;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#ifdef YS_SCANTIME
+    unsigned long long bst[8] = {};
+#endif
+    YS_BSTAMP(0);
+    // Fused path, programmatic dependent launch: this grid becomes resident while k_pack_gt still runs.  The blocks of
+    // the first io.n_identity images (launch order == image index for them, by agreement with k_pack_gt: about one
+    // wave of blocks) do not need anything k_pack_gt writes until after the decode, so they fetch and decode their
+    // tile first and wait for k_pack_gt then; every other block waits here (it needs the image order).
+    const bool early = FUSED && (int)blockIdx.y < io.n_identity;
     if (FUSED) {
-        // programmatic dependent launch: let k_loss_stream become resident behind this grid's last wave, and wait here
-        // for k_pack_gt (whose outputs -- image order, GT lists -- are read from the next line on)
-        cudaTriggerProgrammaticLaunchCompletion();
-        cudaGridDependencySynchronize();
+        cudaTriggerProgrammaticLaunchCompletion();      // k_loss_stream may become resident behind this grid's last wave
+        if (!early) cudaGridDependencySynchronize();
 #ifdef YS_FIXTIME
         if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
             unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
@@ -284,10 +314,11 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         }
 #endif
     }
-    const int b = (FUSED && io.img_order) ? io.img_order[blockIdx.y] : (int)blockIdx.y;
+    YS_BSTAMP(1);
+    const int b = (FUSED && io.img_order && !early) ? io.img_order[blockIdx.y] : (int)blockIdx.y;
     // fused: blocks are cut per level (a block never straddles two levels: one tensor operation loads its tile)
     int lvl = 0, i_lvl = 0, a;
-    bool live;
+    bool live, warp_cols = false;
     if (FUSED) {
 #pragma unroll
         for (int k = 1; k < YS_MAX_LEVELS; ++k)
@@ -296,23 +327,28 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         i_lvl = i0 + tid;
         live = i_lvl < L.hw[lvl];
         a = L.a_off[lvl] + i_lvl;
-        if (tid == 0) {
-            const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_mbar);
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        // each warp feeds itself: lane 0 starts the first kScanStages sides of the warp's 32 anchors
+        warp_cols = i0 + 32 * warp < L.hw[lvl];
+        if (lane == 0 && warp_cols) {
+#pragma unroll
+            for (int s = 0; s < kScanStages; ++s) {
+                const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_mbar[warp][s]);
+                asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            }
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kScanTileBytes) : "memory");
-            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                         ::"r"((unsigned)__cvta_generic_to_shared(s_dyn)), "l"(&M.lvl[lvl]), "r"(i0), "r"(b * L.C), "r"(bar) : "memory");
+#pragma unroll
+            for (int s = 0; s < kScanStages && s < 4; ++s) scan_issue_side(s_dyn, &s_mbar[warp][s], &M.lvl[lvl], warp, s, s, i0, b * L.C);
         }
+        __syncwarp();
     } else {
         a = blockIdx.x * kScanThreads + tid;
         live = a < L.A;
     }
 
-    int g0, n;
-    gt_range<FUSED>(io, b, g0, n);
-    const int ntiles = (n + kGtTile - 1) / kGtTile;
-    const bool one_tile = ntiles <= 1;
+    int g0 = 0, n = 0;
+    if (!early) gt_range<FUSED>(io, b, g0, n);
+    int ntiles = (n + kGtTile - 1) / kGtTile;
+    bool one_tile = ntiles <= 1;
     // GT tile -> shared memory (no barriers inside; the caller brackets it)
     auto stage_gt = [&](int t0, int tn) {
         for (int j = tid; j < tn; j += kScanThreads) {
@@ -329,7 +365,7 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     // GT tile 0: one GT per thread goes into a register now and into shared memory after the decode below, so the
     // latency of this (dependent) load hides under the decode instead of in front of a barrier
     static_assert(kGtTile <= kScanThreads, "tile 0 is staged one GT per thread");
-    const int tn0 = ntiles > 0 ? min(kGtTile, n) : 0;
+    int tn0 = ntiles > 0 ? min(kGtTile, n) : 0;
     float4 q_pre = make_float4(0.f, 0.f, 0.f, 0.f);
     bool v_pre = true;
     if (tid < tn0) {
@@ -341,29 +377,38 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
     float ax = 0.f, ay = 0.f;
     if (FUSED) {
-        {
-            const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_mbar);
-            unsigned ok;
-            do {
-                asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}\n"
-                             : "=r"(ok) : "r"(bar) : "memory");
-            } while (!ok);
+        float d[4] = {0.f, 0.f, 0.f, 0.f};
+        if (warp_cols) {
+            const int i0 = i_lvl - tid;
+#pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                const int st = s % kScanStages;
+                const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_mbar[warp][st]);
+                const unsigned parity = (unsigned)((s / kScanStages) & 1);
+                unsigned ok;
+                do {
+                    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+                } while (!ok);
+                const float *col = reinterpret_cast<const float *>(s_dyn + (size_t)(warp * kScanStages + st) * kScanSideBytes) + lane;
+                float z[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) z[j] = col[j * 32];
+                if (s + kScanStages < 4) {           // the stage is free again: refill it with side s + kScanStages
+                    __syncwarp();
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    if (lane == 0) scan_issue_side(s_dyn, &s_mbar[warp][st], &M.lvl[lvl], warp, st, s + kScanStages, i0, b * L.C);
+                }
+                float m2, inv_s;
+                d[s] = dfl_stats16(z, m2, inv_s);
+            }
         }
+        YS_BSTAMP(2);
         if (live) {
             const int w = L.w[lvl];
             const float st = L.stride[lvl];
             const int iy = i_lvl / w, ix = i_lvl - iy * w;
             const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
-            const float *col = reinterpret_cast<const float *>(s_dyn) + tid;
-            float d[4];
-#pragma unroll
-            for (int s = 0; s < 4; ++s) {
-                float z[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j) z[j] = col[(s * 16 + j) * kScanThreads];
-                float m2, inv_s;
-                d[s] = dfl_stats16(z, m2, inv_s);
-            }
             // dist2bbox in grid units, then * stride (losses/yolo_v8_loss.py:558-559, :412)
             p.x = YS_MUL(YS_SUB(gx, d[0]), st);
             p.y = YS_MUL(YS_SUB(gy, d[1]), st);
@@ -379,6 +424,14 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         ax = c.x;
         ay = c.y;
     }
+    if (early) {               // k_pack_gt's outputs from here on
+        cudaGridDependencySynchronize();
+        gt_range<FUSED>(io, b, g0, n);
+        ntiles = (n + kGtTile - 1) / kGtTile;
+        one_tile = ntiles <= 1;
+        tn0 = ntiles > 0 ? min(kGtTile, n) : 0;
+        if (tid < tn0) q_pre = io.gt_box[g0 + tid];
+    }
     if (tid < tn0) {
         S.box[tid] = q_pre;
         S.area[tid] = area_eps_h(q_pre.x, q_pre.y, q_pre.z, q_pre.w);
@@ -388,6 +441,7 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         S.valid[tid] = v_pre ? 1 : 0;
     }
     __syncthreads();
+    YS_BSTAMP(3);
     const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
     // bounding box of this warp's anchor centres (non-live lanes neutral); order-preserving float <-> uint map so
     // that the dense entry point may be given any (also negative) anchor points
@@ -510,6 +564,7 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         }
     }
 
+    YS_BSTAMP(4);
     // ---- preliminary per-anchor resolve (no forced entries yet): losses/yolo_v8_loss.py:226-244
     int g = -1;
     float ov = 0.f;
@@ -552,13 +607,22 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     }
 
     // ---- last block of this image runs the fix-up
+    YS_BSTAMP(5);
     __threadfence();
     __syncthreads();
+    YS_BSTAMP(6);
     if (tid == 0) {
         const unsigned prev = atomicAdd(&io.img_done[b], 1u);
         s_flag = (prev == gridDim.x - 1u);
     }
     __syncthreads();
+    YS_BSTAMP(7);
+#ifdef YS_SCANTIME
+    if (tid == 0 && (blockIdx.x + blockIdx.y * gridDim.x) % 23 == 0)
+        printf("BLK x=%d y=%d n=%d t0=%llu sync=%llu tma=%llu dec=%llu scan=%llu res=%llu fence=%llu arr=%llu\n", (int)blockIdx.x,
+               (int)blockIdx.y, n, bst[0], bst[1] - bst[0], bst[2] - bst[1], bst[3] - bst[2], bst[4] - bst[3], bst[5] - bst[4],
+               bst[6] - bst[5], bst[7] - bst[6]);
+#endif
     if (!s_flag) return;
     __threadfence();
     if (io.skip_fixup) {

@@ -42,7 +42,8 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
           int N, int B, int nc, float sx, float sy, int *__restrict__ gt_off, int *__restrict__ rank,
           int *__restrict__ cursor_g, float4 *__restrict__ gt_box, int *__restrict__ gt_label,
           unsigned char *__restrict__ risk, unsigned long long *__restrict__ best_key, int *__restrict__ owned_cnt,
-          int *__restrict__ gt_flags, unsigned *__restrict__ counters, int n_counters, int *__restrict__ img_order) {
+          int *__restrict__ gt_flags, unsigned *__restrict__ counters, int n_counters, int *__restrict__ img_order,
+          int n_identity) {
     __shared__ int s_cursor[kPackSmemB];
     __shared__ int s_weight[kOrderMaxB];
     __shared__ int s_part[kPackThreads / 32];
@@ -192,11 +193,11 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
     // after it.  A scheduling hint only: results do not depend on the order.
     __syncthreads();
     for (int b = tid; b < B; b += kPackThreads) {
-        int r = b;
-        if (B <= kOrderMaxB) {
+        int r = b;       // the first n_identity slots keep their own image (k_assign decodes those before it may read this)
+        if (B <= kOrderMaxB && b >= n_identity) {
             const int wb = s_weight[b];
-            r = 0;
-            for (int o = 0; o < B; ++o) {
+            r = n_identity;
+            for (int o = n_identity; o < B; ++o) {
                 const int wo = s_weight[o];
                 r += (wo > wb || (wo == wb && o < b)) ? 1 : 0;
             }
@@ -217,7 +218,7 @@ k_pack_gt_small(LevelSet L, const long long *__restrict__ batch_idx, const long 
                 const float4 *__restrict__ bboxes, int N, int B, int nc, float sx, float sy, int *__restrict__ gt_off,
                 float4 *__restrict__ gt_box, int *__restrict__ gt_label, unsigned char *__restrict__ risk,
                 unsigned long long *__restrict__ best_key, int *__restrict__ owned_cnt, int *__restrict__ gt_flags,
-                unsigned *__restrict__ counters, int n_counters, int *__restrict__ img_order) {
+                unsigned *__restrict__ counters, int n_counters, int *__restrict__ img_order, int n_identity) {
     __shared__ int s_id[kSmallMax];          // image of source row i (-1: ignored)
     __shared__ int s_cnt[kSmallMax];         // GT per image, then reused as launch weights
     __shared__ int s_off[kSmallMax + 1];     // exclusive scan of the counts
@@ -318,11 +319,14 @@ k_pack_gt_small(LevelSet L, const long long *__restrict__ batch_idx, const long 
     __syncthreads();
     // ---- launch order of the images in k_assign: heaviest expected fix-up first (a scheduling hint only)
     if (tid < B) {
-        const int wb = s_cnt[tid];
-        int r = 0;
-        for (int o = 0; o < B; ++o) {
-            const int wo = s_cnt[o];
-            r += (wo > wb || (wo == wb && o < tid)) ? 1 : 0;
+        int r = tid;     // the first n_identity slots keep their own image (k_assign decodes those before it may read this)
+        if (tid >= n_identity) {
+            const int wb = s_cnt[tid];
+            r = n_identity;
+            for (int o = n_identity; o < B; ++o) {
+                const int wo = s_cnt[o];
+                r += (wo > wb || (wo == wb && o < tid)) ? 1 : 0;
+            }
         }
         img_order[r] = tid;
     }
@@ -753,7 +757,7 @@ static int build_scan_maps(ScanMaps &M, const LevelSet &L, int B) {
         const cuuint64_t gdim[2] = {(cuuint64_t)L.hw[l], (cuuint64_t)B * (cuuint64_t)L.C};
         const cuuint64_t gstride[1] = {(cuuint64_t)L.hw[l] * 4u};
         const cuuint32_t estr[2] = {1u, 1u};
-        const cuuint32_t box[2] = {(cuuint32_t)kScanThreads, 64u};
+        const cuuint32_t box[2] = {32u, 16u};       // one side (16 DFL bins) of one warp's 32 anchors
         CUresult r = encode(&M.lvl[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)L.x[l], gdim, gstride, box, estr,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -862,17 +866,34 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     if (norm_out) { YS_REQUIRE(((uintptr_t)norm_out & 15) == 0, YS_ERR_BAD_ARG, "norm must be 16-byte aligned"); }
 
     if ((stages & YS_STAGE_ALL) == 0) stages |= YS_STAGE_ALL;
+    // k_assign's first wave of blocks (3 per SM: its 64 KB tile) decodes before it may read k_pack_gt's image order; the
+    // images of those launch slots are therefore fixed to 0..n_identity-1 (a function of the shapes only)
+    int n_identity = 0;
+    {
+        static int s_sms = 0;
+        if (s_sms == 0) {
+            int dev = 0;
+            if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&s_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || s_sms <= 0)
+                s_sms = 148;
+        }
+        const int wave = 3 * s_sms;
+        n_identity = (wave + L.n_sblk - 1) / L.n_sblk;
+        if (n_identity > B) n_identity = B;
+#ifdef YS_NO_EARLY       // experiment: every block waits for k_pack_gt first
+        n_identity = 0;
+#endif
+    }
     if (stages & YS_STAGE_PACK) {
         if (n_gt <= kSmallMax && B <= kSmallMax)
             k_pack_gt_small<<<1, kSmallMax, 0, stream>>>(L, (const long long *)batch_idx, (const long long *)cls,
                                                         (const float4 *)bboxes, n_gt, B, nc, scale_x, scale_y, W.gt_off,
                                                         W.gt_box, W.gt_label, W.risk, W.best_key, W.owned_cnt,
-                                                        W.gt_flags, W.counters, B + 2, W.img_order);
+                                                        W.gt_flags, W.counters, B + 2, W.img_order, n_identity);
         else
         k_pack_gt<<<1, kPackThreads, 0, stream>>>(L, (const long long *)batch_idx, (const long long *)cls,
                                                   (const float4 *)bboxes, n_gt, B, nc, scale_x, scale_y, W.gt_off, W.rank,
                                                   W.cursor, W.gt_box, W.gt_label, W.risk, W.best_key, W.owned_cnt,
-                                                  W.gt_flags, W.counters, B + 2, W.img_order);
+                                                  W.gt_flags, W.counters, B + 2, W.img_order, n_identity);
         YS_CHECK_LAUNCH("k_pack_gt");
     }
 
@@ -884,6 +905,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
 #ifdef YS_NO_ORDER
     io.img_order = nullptr;
 #endif
+    io.n_identity = io.img_order ? n_identity : B;
     io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
     io.pbox = pred_boxes_px ? (float4 *)pred_boxes_px : W.pbox;
     io.tgi = target_gt_idx ? (int *)target_gt_idx : W.tgi;
@@ -1054,7 +1076,7 @@ extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, co
     io.gt_off = nullptr; io.G = G; io.gt_box = (const float4 *)gt_bboxes; io.gt_label_i = nullptr;
     io.gt_label_f = gt_labels; io.gt_valid = mask_gt; io.pd_box = (const float4 *)pd_bboxes; io.pd_scores = pd_scores;
     io.anc = (const float2 *)anc_points; io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags;
-    io.img_order = nullptr; io.skip_fixup = 0;
+    io.img_order = nullptr; io.n_identity = 0; io.skip_fixup = 0;
     io.forced = W.forced; io.pbox = nullptr; io.tgi = W.tgi; io.lab = nullptr; io.norm = norm_out ? norm_out : W.norm;
     io.partial = W.scan_partial; io.img_sum = W.img_sum; io.tss = W.tss;
     io.done_counter = W.counters; io.img_done = W.counters + 2;
