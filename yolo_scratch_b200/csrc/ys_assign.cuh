@@ -213,14 +213,28 @@ __device__ __forceinline__ int resolve_row_group(const AssignIO &io, const Level
         area_p = area_eps_h(p.x, p.y, p.z, p.w);
         float best_ov = -1.f;      // this lane's first maximum (ascending j)
         int best_j = 0;
-#pragma unroll 4
-        for (int j = sub; j < n; j += W) {
-            const float4 q = io.gt_box[g0 + j];
-            const float ov = iou_assign_lazy(p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
-            const bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
-            const bool m = (centre_in_box(ax, ay, q) && valid) || forced[2 * j] == k || forced[2 * j + 1] == k;
-            if (m) { ++cnt; first = min(first, (unsigned)j); }
-            if (ov > best_ov) { best_ov = ov; best_j = j; }
+        // four GT per trip, their loads issued together (the loop is latency-bound: one warp, dependent loads)
+        for (int j0 = sub; j0 < n; j0 += 4 * W) {
+            float4 q[4];
+            int2 f[4];
+            bool valid[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int jc = min(j0 + u * W, n - 1);
+                q[u] = io.gt_box[g0 + jc];
+                f[u] = *reinterpret_cast<const int2 *>(forced + 2 * jc);
+                valid[u] = FUSED ? true : (io.gt_valid[g0 + jc] != 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = j0 + u * W;
+                if (j < n) {
+                    const float ov = iou_assign_lazy(p, area_p, q[u], area_eps_h(q[u].x, q[u].y, q[u].z, q[u].w));
+                    const bool m = (centre_in_box(ax, ay, q[u]) && valid[u]) || f[u].x == k || f[u].y == k;
+                    if (m) { ++cnt; first = min(first, (unsigned)j); }
+                    if (ov > best_ov) { best_ov = ov; best_j = j; }
+                }
+            }
         }
         if (best_ov >= 0.f) best = argmax_key(best_ov, (unsigned)best_j);
     }
@@ -705,6 +719,10 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
     unsigned long long stamp[8] = {};
 #endif
     YS_STAMP(0);
+    // the image's scan partials (independent of the fix-up): warp 0 fetches them now, their latency hides under phase A
+    double acc = 0.0;
+    if (warp == 0)
+        for (int i = lane; i < nblk; i += 32) acc += (double)__ldcg(io.partial + (size_t)b * nblk + i);
     if (tid == 0) { s_nneedy = 0; s_ncmp = 0; s_nlost = 0; s_nuniq = 0; s_nlonely = 0; s_nfired = 0; }
     if (tid < kWarps) s_delta[tid] = 0.0;
     __syncthreads();
@@ -912,9 +930,8 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
     }
     // ---- per-image sum of target scores (fixed order), then target_scores_sum in the last image
     if (warp == 0) {
-        double acc = 0.0;
-        for (int i = lane; i < nblk; i += 32) acc += (double)__ldcg(io.partial + (size_t)b * nblk + i);
         acc = warp_sum(acc);
+        unsigned prev = 0u;
         if (lane == 0) {
             double dsum = 0.0;
 #pragma unroll
@@ -922,11 +939,15 @@ __device__ void fixup_image(const LevelSet &L, const AssignIO &io, int b, int B,
             io.img_sum[b] = acc + dsum;
             io.img_done[b] = 0u;
             __threadfence();
-            const unsigned prev = atomicAdd(io.done_counter, 1u);
-            if (prev == (unsigned)B - 1u) {
-                __threadfence();
-                double tot = 0.0;
-                for (int i = 0; i < B; ++i) tot += __ldcg(io.img_sum + i);
+            prev = atomicAdd(io.done_counter, 1u);
+        }
+        prev = __shfl_sync(0xffffffffu, prev, 0);
+        if (prev == (unsigned)B - 1u) {                // last image of the batch: target_scores_sum, lanes over the images
+            __threadfence();
+            double tot = 0.0;
+            for (int i = lane; i < B; i += 32) tot += __ldcg(io.img_sum + i);
+            tot = warp_sum(tot);
+            if (lane == 0) {
                 const float tss = (float)tot;
                 io.tss[0] = tss > 1.f ? tss : 1.f;     // max(target_scores.sum(), 1)  (:472)
                 *io.done_counter = 0u;
