@@ -866,8 +866,11 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     if (norm_out) { YS_REQUIRE(((uintptr_t)norm_out & 15) == 0, YS_ERR_BAD_ARG, "norm must be 16-byte aligned"); }
 
     if ((stages & YS_STAGE_ALL) == 0) stages |= YS_STAGE_ALL;
-    // k_assign's first wave of blocks (3 per SM: its 64 KB tile) decodes before it may read k_pack_gt's image order; the
+    // k_assign's first wave of blocks (YS_SCAN_MINBLOCKS per SM) decodes before it may read k_pack_gt's image order; the
     // images of those launch slots are therefore fixed to 0..n_identity-1 (a function of the shapes only)
+#ifndef YS_IDENTITY_WAVE
+#define YS_IDENTITY_WAVE YS_SCAN_MINBLOCKS      // resident k_assign blocks per SM
+#endif
     int n_identity = 0;
     {
         static int s_sms = 0;
@@ -876,7 +879,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
             if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&s_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || s_sms <= 0)
                 s_sms = 148;
         }
-        const int wave = 3 * s_sms;
+        const int wave = YS_IDENTITY_WAVE * s_sms;
         n_identity = (wave + L.n_sblk - 1) / L.n_sblk;
         if (n_identity > B) n_identity = B;
 #ifdef YS_NO_EARLY       // experiment: every block waits for k_pack_gt first
