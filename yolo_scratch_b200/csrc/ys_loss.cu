@@ -25,15 +25,14 @@ constexpr int kRiskMaxCentres = YS_RISK_MAX_CENTRES;
 constexpr int kContainMaxGt = 64;     // images with at most this many GT get the containment hint
 constexpr int kOrderMaxB = 1024;      // batches up to this size get their images ordered "fix-up likely" first   // GT with at most this many anchor centres inside get their best-IoU anchor from the scan
 
-// Number of grid centres c_i = (i + 0.5) * stride, i in [0, n), strictly inside (lo, hi) by the reference's test
-// (c - lo > 1e-9 and hi - c > 1e-9, losses/yolo_v8_loss.py:220-224).  Both predicates are monotonic in i, so the
-// first and last index are found by a short exact walk from an estimate.
+// Number of grid centres c_i = (i + 0.5) * stride, i in [0, n), inside (lo, hi): an ESTIMATE (a centre sitting on an
+// edge may be counted either way).  It only feeds k_assign's launch-order hint, never a result, and k_pack_gt is one
+// block that runs once per step with a cold instruction cache -- the exact edge walk that used to be here cost 5 us
+// of the step's critical path.
 __device__ __forceinline__ int centres_inside(float lo, float hi, int n, float stride) {
-    int i0 = (int)floorf(lo / stride - 0.5f) - 1, i1 = (int)ceilf(hi / stride - 0.5f) + 1;
-    i0 = min(max(i0, 0), n);
-    i1 = max(min(i1, n - 1), -1);
-    while (i0 < n && !(YS_SUB(YS_MUL((float)i0 + 0.5f, stride), lo) > kEpsInBox)) ++i0;
-    while (i1 >= 0 && !(YS_SUB(hi, YS_MUL((float)i1 + 0.5f, stride)) > kEpsInBox)) --i1;
+    const float inv = __frcp_rn(stride);
+    const int i0 = max((int)floorf(lo * inv - 0.5f) + 1, 0);
+    const int i1 = min((int)ceilf(hi * inv - 0.5f) - 1, n - 1);
     return max(0, i1 - i0 + 1);
 }
 
@@ -161,7 +160,7 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
         // (:117-139, :146-162) can fire for; the scan computes their best-IoU anchor on the way.
         int centres = 0;
         for (int l = 0; l < L.n && centres <= kRiskMaxCentres; ++l)
-            centres += centres_inside(qp.x, qp.z, L.w[l], L.stride[l]) * centres_inside(qp.y, qp.w, L.hw[l] / L.w[l], L.stride[l]);
+            centres += centres_inside(qp.x, qp.z, L.w[l], L.stride[l]) * centres_inside(qp.y, qp.w, (int)((float)L.hw[l] * __frcp_rn((float)L.w[l]) + 0.5f), L.stride[l]);
         risk[dst] = centres <= kRiskMaxCentres ? 1 : 0;
         if (B <= kOrderMaxB && centres <= kRiskMaxCentres) atomicAdd(&s_weight[(int)id], centres <= 4 ? 64 : 1);
         long long c = cls[i];
@@ -294,7 +293,7 @@ k_pack_gt_small(LevelSet L, const long long *__restrict__ batch_idx, const long 
         gt_label[dst] = (int)c;
         int centres = 0;
         for (int l = 0; l < L.n && centres <= kRiskMaxCentres; ++l)
-            centres += centres_inside(qp.x, qp.z, L.w[l], L.stride[l]) * centres_inside(qp.y, qp.w, L.hw[l] / L.w[l], L.stride[l]);
+            centres += centres_inside(qp.x, qp.z, L.w[l], L.stride[l]) * centres_inside(qp.y, qp.w, (int)((float)L.hw[l] * __frcp_rn((float)L.w[l]) + 0.5f), L.stride[l]);
         s_risk[dst] = centres <= kRiskMaxCentres ? (centres <= 4 ? 2 : 1) : 0;
     }
     if (tid < B) s_cnt[tid] = 0;            // from here on: launch weights
