@@ -162,7 +162,7 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
         for (int l = 0; l < L.n && centres <= kRiskMaxCentres; ++l)
             centres += centres_inside(qp.x, qp.z, L.w[l], L.stride[l]) * centres_inside(qp.y, qp.w, (int)((float)L.hw[l] * __frcp_rn((float)L.w[l]) + 0.5f), L.stride[l]);
         risk[dst] = centres <= kRiskMaxCentres ? 1 : 0;
-        if (B <= kOrderMaxB && centres <= kRiskMaxCentres) atomicAdd(&s_weight[(int)id], centres <= 4 ? 64 : 1);
+        if (B <= kOrderMaxB) atomicAdd(&s_weight[(int)id], (centres <= kRiskMaxCentres ? (centres <= 4 ? 64 : 1) : 0) * 2048 + 1);
         long long c = cls[i];
         c = c < 0 ? 0 : (c > nc - 1 ? nc - 1 : c);
         gt_label[dst] = (int)c;
@@ -184,7 +184,7 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
         }
         if (inside) {
             risk[dst] = 1;
-            if (B <= kOrderMaxB) atomicAdd(&s_weight[(int)id], 1);
+            if (B <= kOrderMaxB) atomicAdd(&s_weight[(int)id], 2048);
         }
     }
     // Launch order of the images in k_assign (blockIdx.y -> image): the ones whose forced-assignment fix-up is
@@ -313,7 +313,9 @@ k_pack_gt_small(LevelSet L, const long long *__restrict__ batch_idx, const long 
             if (inside) { rk = 1; wgt = 1; }
         }
         risk[dst] = rk ? 1 : 0;
-        if (wgt) atomicAdd(&s_cnt[id], wgt);
+        // secondary key: the image's GT count (more GT, more arg-max contests lost: ownerless GT are what the hint
+        // cannot see), so the images launched last are the ones with the fewest GT
+        atomicAdd(&s_cnt[id], wgt * 2048 + 1);
     }
     __syncthreads();
     // ---- launch order of the images in k_assign: heaviest expected fix-up first (a scheduling hint only)
