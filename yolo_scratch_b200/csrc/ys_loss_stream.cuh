@@ -3,7 +3,7 @@
 // Same arithmetic as k_loss (ys_loss.cu) -- BCE-with-logits, CIoU and DFL, forward and backward, replacing
 // losses/yolo_v8_loss.py:472-499 and :280-324 of the reference plus their autograd backward -- but the head values
 // are no longer loaded into registers by the warp that consumes them.  k_loss is latency bound (64 registers x
-// 32 warps per SM leave ~40 KB of loads in flight per SM); here every warp owns a two-stage ring of 4 KB
+// 32 warps per SM leave ~40 KB of loads in flight per SM); here every warp owns a two- or three-stage ring of 4-5 KB
 // shared-memory tiles filled by bulk asynchronous copies (cp.async.bulk global -> shared, completion on an
 // mbarrier), so the tile of work item k+1 is in flight -- costing no registers -- while item k is computed:
 // 16 warps x 5 KB = 80 KB in flight per SM at all times.
@@ -31,7 +31,7 @@ namespace ys {
 #endif
 constexpr int kStreamWarps = YS_STREAM_WARPS;
 constexpr int kStreamThreads = kStreamWarps * 32;
-constexpr int kStreamStages = 2;
+constexpr int kStreamStagesMax = 3;      // tiles per warp ring (template parameter STAGES = 2 or 3): one being computed, the others in flight
 constexpr int kBoxItem = 16;             // anchors per box item
 #ifndef YS_CLS_ROWS
 #define YS_CLS_ROWS 10
@@ -143,6 +143,23 @@ __device__ __forceinline__ Item decode_item(const LevelSet &L, const StreamParam
         it.n_live = min(kChunk, it.hw - it.i0);
     }
     it.l = l;
+    return it;
+}
+
+// Queue entry of the pipeline: an Item in three registers (meta = (group + 1) << 12 | level << 8 | n_live).
+struct ItemQ {
+    int b, i0, meta;
+};
+__device__ __forceinline__ ItemQ pack_item(const Item &it) {
+    ItemQ q;
+    q.b = it.b; q.i0 = it.i0; q.meta = ((it.group + 1) << 12) | (it.l << 8) | it.n_live;
+    return q;
+}
+__device__ __forceinline__ Item unpack_item(const LevelSet &L, const ItemQ &q) {
+    Item it;
+    it.b = q.b; it.i0 = q.i0;
+    it.n_live = q.meta & 255; it.l = (q.meta >> 8) & 15; it.group = (q.meta >> 12) - 1;
+    it.hw = it.n_live > 0 ? L.hw[it.l] : 0;
     return it;
 }
 
@@ -318,17 +335,17 @@ __device__ __forceinline__ void stream_cls(const LevelSet &L, const StreamParams
 }
 
 // ---- kernel ---------------------------------------------------------------------------------------------------
-template <bool WRITE_GRAD>
+template <bool WRITE_GRAD, int STAGES>
 __global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, StreamParams P, const __grid_constant__ StreamMaps M) {
     extern __shared__ __align__(128) char s_ring[];                 // [warp][stage][kStageBytes]
-    __shared__ __align__(8) unsigned long long s_bar[kStreamWarps][kStreamStages];
+    __shared__ __align__(8) unsigned long long s_bar[kStreamWarps][kStreamStagesMax];
     __shared__ float s_sum[kStreamWarps][3];
     __shared__ double s_fin[kStreamWarps][3];
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (lane == 0) {
 #pragma unroll
-        for (int s = 0; s < kStreamStages; ++s) mbar_init(smem_u32(&s_bar[warp][s]), 1u);
+        for (int s = 0; s < STAGES; ++s) mbar_init(smem_u32(&s_bar[warp][s]), 1u);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
@@ -337,7 +354,7 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, S
     cudaGridDependencySynchronize();
     const float inv_tss = 1.0f / P.tss[0];
     float acc_box = 0.f, acc_cls = 0.f, acc_dfl = 0.f;
-    char *ring = s_ring + (size_t)warp * kStreamStages * kStageBytes;
+    char *ring = s_ring + (size_t)warp * STAGES * kStageBytes;
     const int step = (int)gridDim.x * kStreamWarps;
     int item = (int)blockIdx.x * kStreamWarps + warp;
 
@@ -373,6 +390,62 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, S
         return g < P.n_groups16 ? (int)(g * kStreamWarps) + warp : P.total_items;      // past the end: padding item
     };
     auto load_tg2 = [&](const Item &it) -> int { return it.n_live > 0 ? load_tg(it) : -1; };
+    if (STAGES == 3) {
+    // Three stages: while item k is computed, the tiles of items k+1 and k+2 are in flight and the assignment lookup of
+    // k+3 is on its way.  With two stages a cheap item (an all-background box item: eight stores) left the next tile
+    // ~0.2 us to arrive and the warp then sat in mbar_wait (14 % of all warp samples).  The queue holds packed items.
+    {
+        ItemQ q0 = {0, 0, 0}, q1 = q0, q2 = q0, q3 = q0;
+        int t0 = -1, t1 = -1, t2 = -1, t3 = -1;
+        bool l0 = false, l1 = false;
+        auto loaded_of = [&](const ItemQ &q, int tg) -> bool {
+            return (q.meta & 255) > 0 && ((q.meta >> 12) > 0 || __any_sync(0xffffffffu, tg >= 0));
+        };
+        auto fetch = [&](ItemQ &q, int &tg) {
+            const Item it = decode_item(L, P, next_group_item());
+            tg = load_tg2(it);
+            q = pack_item(it);
+        };
+        if (my_groups > 0u) {
+            fetch(q0, t0);
+            l0 = loaded_of(q0, t0);
+            if (l0) issue_item(L, P, M, unpack_item(L, q0), ring, smem_u32(&s_bar[warp][0]), lane);
+        }
+        if (my_groups > 1u) {
+            fetch(q1, t1);
+            l1 = loaded_of(q1, t1);
+            if (l1) issue_item(L, P, M, unpack_item(L, q1), ring + kStageBytes, smem_u32(&s_bar[warp][1]), lane);
+        }
+        if (my_groups > 2u) fetch(q2, t2);
+        (void)item; (void)step; (void)cur; (void)nxt; (void)nn; (void)tg_cur; (void)tg_nxt; (void)tg_nn; (void)cur_loaded; (void)nxt_loaded;
+        int s = 0;
+        for (unsigned k = 0; k < my_groups; ++k) {
+            const int s2 = s >= 1 ? s - 1 : 2;          // (s + 2) % 3: the stage item k-1 just left
+            bool l2 = false;
+            if (k + 2u < my_groups) {
+                l2 = loaded_of(q2, t2);
+                __syncwarp();
+                fence_async_smem();
+                if (l2) issue_item(L, P, M, unpack_item(L, q2), ring + (size_t)s2 * kStageBytes, smem_u32(&s_bar[warp][s2]), lane);
+                if (k + 3u < my_groups) fetch(q3, t3);
+            }
+            const char *stage = ring + (size_t)s * kStageBytes;
+            const Item it = unpack_item(L, q0);
+            if (l0) {
+                mbar_wait(smem_u32(&s_bar[warp][s]), (phase_bits >> s) & 1u);
+                phase_bits ^= 1u << s;
+                if (it.group >= 0) stream_cls<WRITE_GRAD>(L, P, it, stage, lane, inv_tss, acc_cls);
+                else stream_box<WRITE_GRAD>(L, P, it, stage, t0, lane, inv_tss, acc_box, acc_dfl);
+            } else if (it.n_live > 0) {
+                stream_box_zero<WRITE_GRAD>(L, it, lane);
+            }
+            q0 = q1; t0 = t1; l0 = l1;
+            q1 = q2; t1 = t2; l1 = l2;
+            q2 = q3; t2 = t3;
+            s = s == 2 ? 0 : s + 1;
+        }
+    }
+    } else {
     if (my_groups > 0u) {
         cur = decode_item(L, P, next_group_item());
         tg_cur = load_tg2(cur);
@@ -411,6 +484,8 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, S
         }
         cur = nxt; tg_cur = tg_nxt; cur_loaded = nxt_loaded;
         nxt = nn; tg_nxt = tg_nn;
+    }
+
     }
 
     // ------------------------------------------------------------------ CTA partial sums (fixed order)
