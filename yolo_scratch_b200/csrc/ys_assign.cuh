@@ -26,7 +26,10 @@ namespace ys {
 #define YS_SCAN_MINBLOCKS 4
 #endif
 constexpr int kScanThreads = YS_SCAN_THREADS;
-constexpr int kGtTile = kScanThreads < 256 ? kScanThreads : 256;        // GT boxes staged per shared-memory tile
+#ifndef YS_GT_TILE
+#define YS_GT_TILE (YS_SCAN_THREADS < 256 ? YS_SCAN_THREADS : 256)
+#endif
+constexpr int kGtTile = YS_GT_TILE;        // GT boxes staged per shared-memory tile
 constexpr int kFixSmemGt = 256;     // per-image GT count the fix-up handles with shared-memory scratch (dense entry point)
 #ifndef YS_SCAN_STAGES
 #define YS_SCAN_STAGES 2

@@ -909,7 +909,9 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
 #ifdef YS_NO_ORDER
     io.img_order = nullptr;
 #endif
-    io.n_identity = io.img_order ? n_identity : B;
+    // decode-before-wait is only sound behind this call's own k_pack_gt (an ordinary launch: everything earlier in the
+    // stream, the producer of the head outputs included, has completed before it starts)
+    io.n_identity = (stages & YS_STAGE_PACK) ? (io.img_order ? n_identity : B) : 0;
     io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
     io.pbox = pred_boxes_px ? (float4 *)pred_boxes_px : W.pbox;
     io.tgi = target_gt_idx ? (int *)target_gt_idx : W.tgi;
