@@ -92,13 +92,20 @@ def test_loss_dense_scene_vs_oracle(cuda_lib, seed, B, imgsz, kw):
     spliced_case(seed, B, imgsz, kw.get("fixed_count", 20), kw)
 
 
-def spliced_case(seed, B, imgsz, max_gt, kw):
+@pytest.mark.parametrize("seed,nc", [(220, 1), (221, 13), (222, 23)])
+def test_loss_vs_oracle_other_class_counts(cuda_lib, seed, nc):
+    """Class counts that are not a multiple of the class rows per work item (10): one partial group (nc = 1), a full
+    and a partial one (13), two full and a partial one (23)."""
+    spliced_case(seed, 2, 320, 12, {"p_nested": 0.2}, nc=nc)
+
+
+def spliced_case(seed, B, imgsz, max_gt, kw, nc=80):
     from oracle import ref_port as orc
-    feats = synth.make_head_levels(B, imgsz, 80, 16, seed=seed)
-    batch = synth.make_gt_batch(B, 80, max_gt, seed=seed + 1, imgsz=imgsz, **kw)
-    total, items, grads, crit = run_cuda(feats, batch, 80, export=True)
+    feats = synth.make_head_levels(B, imgsz, nc, 16, seed=seed)
+    batch = synth.make_gt_batch(B, nc, max_gt, seed=seed + 1, imgsz=imgsz, **kw)
+    total, items, grads, crit = run_cuda(feats, batch, nc, export=True)
     leaves = [f.clone().requires_grad_(True) for f in feats]
-    rtotal, ritems, parts = orc.detection_loss(leaves, batch, 80, 16, synth.LEVEL_STRIDES, return_parts=True)
+    rtotal, ritems, parts = orc.detection_loss(leaves, batch, nc, 16, synth.LEVEL_STRIDES, return_parts=True)
     rtotal.backward()
     ex = {k: v.cpu() for k, v in crit.last_export.items()}
     # (1) decoded boxes to 1e-6 of the image size
@@ -107,11 +114,11 @@ def spliced_case(seed, B, imgsz, max_gt, kw):
     A = ex["pred_bboxes_px"].shape[1]
     tg = orc.pack_targets(batch["cls"], batch["bboxes"], batch["batch_idx"], B, torch.tensor([float(imgsz), float(imgsz)]))
     anc, st = orc.anchors_for([f.shape[2:] for f in feats], synth.LEVEL_STRIDES)
-    flat = torch.cat([f.view(B, 144, -1) for f in feats], 2)
+    flat = torch.cat([f.view(B, 64 + nc, -1) for f in feats], 2)
     scores = flat[:, 64:].permute(0, 2, 1).sigmoid()
     if tg.shape[1] > 0:
         _, _, _, fg, tgi = orc.assign(scores, ex["pred_bboxes_px"], anc * st, tg[..., 0], tg[..., 1:5],
-                                      (tg[..., 5] > 0).float(), 80)
+                                      (tg[..., 5] > 0).float(), nc)
         ours_fg = ex["target_gt_idx"] >= 0
         assert torch.equal(ours_fg, fg.bool())
         assert torch.equal(ex["target_gt_idx"].clamp(min=0).long(), tgi)
