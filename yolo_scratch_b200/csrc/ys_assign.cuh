@@ -625,10 +625,12 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
 
     // ---- last block of this image runs the fix-up
     YS_BSTAMP(5);
-    __threadfence();
+    // release pattern of a grid barrier: block barrier first, then ONE thread fences (cumulative over the writes the
+    // barrier ordered before it) and arrives -- 255 fewer MEMBARs per block than fencing in every thread
     __syncthreads();
     YS_BSTAMP(6);
     if (tid == 0) {
+        __threadfence();
         const unsigned prev = atomicAdd(&io.img_done[b], 1u);
         s_flag = (prev == gridDim.x - 1u);
     }
