@@ -36,7 +36,7 @@ template <int LAYOUT>
 __global__ void __launch_bounds__(kFilterThreads)
 k_nms_filter(const float *__restrict__ pred, int B, int A, int nc, float conf, unsigned long long *__restrict__ keys,
              float4 *__restrict__ boxes, int *__restrict__ cls, int *__restrict__ count) {
-    extern __shared__ float s_rows[];   // LAYOUT 1: per warp 32 rows with odd stride
+    extern __shared__ __align__(16) float s_rows[];   // LAYOUT 1: per warp 32 rows with odd stride
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int warps_per_img = (A + 31) / 32;
     const long long gw = (long long)blockIdx.x * (kFilterThreads / 32) + warp;
@@ -47,7 +47,35 @@ k_nms_filter(const float *__restrict__ pred, int B, int A, int nc, float conf, u
     const int R = 4 + nc;
     float cx = 0.f, cy = 0.f, bw = 0.f, bh = 0.f, best = 0.f;
     int bc = 0;
-    if (LAYOUT == 1) {
+    if (LAYOUT == 1 && (R & 3) == 0 && (reinterpret_cast<uintptr_t>(pred) & 15) == 0) {
+        // Rows of R floats, R a multiple of 4: the warp's 32 rows are one contiguous, 16-byte aligned run of 32*R*4
+        // bytes.  It is copied as float4 (all of a lane's loads in flight together) into shared memory at the same
+        // linear offsets, and every lane then walks ITS row as float4: row stride R/4 float4 (21 at nc = 80, odd ->
+        // the eight lanes of a quarter-warp hit eight different 16-byte bank groups).  The scalar version below
+        // (one division per element, 4-byte loads) ran at 0.78 TB/s.
+        const int R4 = R >> 2;
+        float4 *mine4 = reinterpret_cast<float4 *>(s_rows + (size_t)warp * 32 * (R | 1));      // 128 * (R|1) bytes per warp
+        const int rows = min(32, A - a0);
+        const float4 *src4 = reinterpret_cast<const float4 *>(pred + ((size_t)b * A + a0) * R);
+        const int total4 = rows * R4;
+#pragma unroll 7
+        for (int i = lane; i < total4; i += 32) mine4[i] = __ldg(src4 + i);
+        __syncwarp();
+        if (a < A) {
+            const float4 *row4 = mine4 + lane * R4;
+            const float4 q = row4[0];
+            cx = q.x; cy = q.y; bw = q.z; bh = q.w;
+            best = row4[1].x;                                           // row[4]: the starting value (class 0)
+            for (int j = 1; j < R4; ++j) {
+                const float4 v = row4[j];
+                const int c = (j - 1) * 4;
+                if (v.x > best) { best = v.x; bc = c; }
+                if (v.y > best) { best = v.y; bc = c + 1; }             // first maximum (torch.max(dim) semantics)
+                if (v.z > best) { best = v.z; bc = c + 2; }
+                if (v.w > best) { best = v.w; bc = c + 3; }
+            }
+        }
+    } else if (LAYOUT == 1) {
         const int RS = R | 1;
         float *mine = s_rows + (size_t)warp * 32 * RS;
         const int rows = min(32, A - a0);
