@@ -413,7 +413,7 @@ k_nms_suppress_reg(const int *__restrict__ count, int A, const float4 *__restric
         __syncthreads();
         // -- greedy resolution of the tile by ONE WARP: the 64 row masks live in registers (two per lane), the running
         //    "removed" mask is replicated in every lane, one shuffle per row; then the lanes compact the kept rows for
-        //    the column pass (rows of zero extent -> NaN, padding to a multiple of 8 -> NaN: never a candidate)
+        //    the column pass (rows of zero extent and the padding to a multiple of 8 -> (+inf,+inf,-inf,-inf): never a candidate)
         if (warp == 0) {
             const unsigned long long d0 = lane < tn ? s_diag[lane] : 0ull;
             const unsigned long long d1 = lane + 32 < tn ? s_diag[lane + 32] : 0ull;
@@ -428,20 +428,21 @@ k_nms_suppress_reg(const int *__restrict__ count, int A, const float4 *__restric
                 }
             }
             const int nk = __popcll(kept);
-            const float qnan = __int_as_float(0x7fc00000);
+            const float pinf = __int_as_float(0x7f800000), ninf = __int_as_float(0xff800000);
+            const float4 never = make_float4(pinf, pinf, ninf, ninf);      // x2 - anything = -inf: never a candidate
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int r = lane + 32 * h;
                 if ((kept >> r) & 1ull) {
                     const int pos = __popcll(kept & ((1ull << r) - 1ull));
                     float4 v = s_tile[r];
-                    if (sane && !(v.z > v.x && v.w > v.y)) v = make_float4(qnan, qnan, qnan, qnan);
+                    if (sane && !(v.z > v.x && v.w > v.y)) v = never;
                     s_kbox[pos] = v;
                     s_karea[pos] = s_tarea[r];
                     if (CLASS_AWARE) s_kcls[pos] = s_tcls[r];
                 }
             }
-            if (lane < ((nk + 7) & ~7) - nk) s_kbox[nk + lane] = make_float4(qnan, qnan, qnan, qnan);
+            if (lane < ((nk + 7) & ~7) - nk) s_kbox[nk + lane] = never;
             if (lane == 0) { s_nk = nk; s_trem = rem; }
         }
         __syncthreads();
@@ -460,19 +461,30 @@ k_nms_suppress_reg(const int *__restrict__ count, int A, const float4 *__restric
                     // Branch-free candidate pass: two boxes of positive extent intersect iff
                     //   bi.z > bj.x && bj.z > bi.x && bi.w > bj.y && bj.w > bi.y
                     // (min(a,b) - max(c,d) > 0 in fp32 <=> min(a,b) > max(c,d); the two remaining comparisons, each
-                    // box's own extent, are folded into the data: kept rows of zero extent were stored as NaN, and
+                    // box's own extent, are folded into the data: kept rows of zero extent were stored as (+inf,+inf,-inf,-inf), and
                     // a column of zero extent has ok_j false).  The exact IoU runs only on the candidates.
                     if (bj.z > bj.x && bj.w > bj.y) {
+                        // a > b  <=>  fl(a - b) > 0 for finite fp32 (gradual underflow; under flush-to-zero the sign
+                        // survives), so the four comparisons become four FADDs (fma pipe) and the pair's verdict is
+                        // the OR of the four sign bits (two LOP3) shifted into a mask (one SHF): 3 alu-pipe
+                        // instructions per pair instead of 4 FSETP + SEL + LOP3 -- the alu pipe was the limiter
+                        // (ncu: math-pipe throttle the top stall, 62 % issue).  A difference of +0 (touching boxes)
+                        // reads as a hit: a harmless false candidate, the exact IoU below says 0.
                         unsigned long long cand = 0ull;
-                        for (int q0 = 0; q0 < nk; q0 += 8) {          // s_kbox is padded with NaN rows to a multiple of 8
-                            unsigned m8 = 0u;
+                        for (int q0 = 0; q0 < nk; q0 += 32) {         // s_kbox is padded with never-hit rows to a multiple of 8
+                            const int qe = min(32, ((nk + 7) & ~7) - q0);
+                            unsigned nm = 0u;                          // "no hit" bits, latest pair in bit 0
+                            for (int u0 = 0; u0 < qe; u0 += 8) {
 #pragma unroll
-                            for (int u = 0; u < 8; ++u) {
-                                const float4 bi = s_kbox[q0 + u];
-                                const bool hit = bi.z > bj.x && bj.z > bi.x && bi.w > bj.y && bj.w > bi.y;
-                                m8 |= hit ? (1u << u) : 0u;
+                                for (int u = 0; u < 8; ++u) {
+                                    const float4 bi = s_kbox[q0 + u0 + u];
+                                    const int sg = __float_as_int(__fsub_rn(bi.z, bj.x)) | __float_as_int(__fsub_rn(bj.z, bi.x)) |
+                                                   __float_as_int(__fsub_rn(bi.w, bj.y)) | __float_as_int(__fsub_rn(bj.w, bi.y));
+                                    nm = __funnelshift_l((unsigned)sg, nm, 1);
+                                }
                             }
-                            cand |= (unsigned long long)m8 << q0;
+                            const unsigned hits = (~__brev(nm)) >> (32 - qe);      // pair q0 + i -> bit i
+                            cand |= (unsigned long long)hits << q0;
                         }
                         while (cand && !dead) {
                             const int q = __ffsll((long long)cand) - 1;
