@@ -564,6 +564,331 @@ k_nms_suppress_reg(const int *__restrict__ count, int A, const float4 *__restric
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// k_nms_suppress_zreg: k_nms_suppress_reg with the columns handed to the threads in Z-ORDER of their centres.
+// In k_nms_suppress_reg thread t owns the score ranks t, t+1024, ...: the 32 columns a warp holds in one slot are
+// scattered over the image and every column meets every kept row of a tile (N^2/2 pair tests, ~8 instructions
+// each).  Here the 1024 ranks of a slot are dealt out by a counting sort on the 8-bit Morton key of the box centre
+// (16 x 16 grid over the image's own extent), so a warp's 32 columns of a slot are neighbours; the warp keeps the
+// bounding box of its (shrunken, see nms_shrink_half) columns per slot, and per tile and slot ONE warp-wide test
+// (two rows per lane, two ballots) picks the kept rows that can reach any of them -- the pair loop runs over those
+// only (a few of 64 for COCO-sized boxes).  Which thread holds a column does not enter any verdict: every pair
+// that can suppress is still decided by the same exact IoU, so keep lists are unchanged.
+// Bookkeeping that followed the rank order moves to shared memory: the alive bitmap is indexed by rank (a dying
+// column clears its bit with one atomicAnd; the tile's rows are read from it, and the final compaction too), the
+// tile's boxes are read from the sorted list in global memory (1 KB per tile, L2), and s_perm[slot][thread] gives
+// the rank a thread's column has inside the slot (needed only in the slot the current tile lies in).
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned nms_part1by1_4(unsigned v) {
+    v &= 0xFu;
+    v = (v | (v << 2)) & 0x33u;
+    v = (v | (v << 1)) & 0x55u;
+    return v;
+}
+
+template <bool CLASS_AWARE, int COLS>
+__global__ void __launch_bounds__(kRegThreads, 1)
+k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restrict__ sbox, const float *__restrict__ sscore,
+                    const int *__restrict__ scls, const int *__restrict__ sanchor, float thr, float img_size,
+                    int *__restrict__ keep_anchor, float4 *__restrict__ keep_boxes, float *__restrict__ keep_scores,
+                    int *__restrict__ keep_labels, int *__restrict__ keep_count) {
+    constexpr int kWarps = kRegThreads / 32;
+    __shared__ float4 s_tile[64];
+    __shared__ float s_tarea[64];
+    __shared__ int s_tcls[64];
+    __shared__ unsigned long long s_diag[64];
+    __shared__ float4 s_kbox[64];
+    __shared__ float4 s_kshr[64];
+    __shared__ float s_karea[64];
+    __shared__ int s_kcls[64];
+    __shared__ int s_nk;
+    __shared__ unsigned s_alive[COLS * kWarps];                    // bit per score rank, 1 = alive
+    __shared__ unsigned short s_perm[COLS * kRegThreads];          // [slot][thread] -> rank inside the slot, 0xFFFF = none
+    __shared__ int s_hist[COLS][256];
+    __shared__ float4 s_wbb[COLS][kWarps];                         // per slot and warp: bounding box of the warp's shrunken columns
+    __shared__ float s_red[4][kWarps];
+    const int b = blockIdx.x;
+    const int n = count[b];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (n == 0) {
+        if (tid == 0) keep_count[b] = 0;
+        return;
+    }
+    const float4 *gbox = sbox + (size_t)b * A;
+    const int *gcls = scls + (size_t)b * A;
+    const float pinf = __int_as_float(0x7f800000), ninf = __int_as_float(0xff800000);
+    const float4 never = make_float4(pinf, pinf, ninf, ninf);      // x2 - anything = -inf: never a candidate
+    float4 bx[COLS];
+    int cl[COLS];
+    bool sane = true;      // finite, well-formed boxes: a pair that does not intersect then has IoU exactly 0
+    // ---- pass 1 (rank order): sanity and the extent of the centres
+    float mnx = pinf, mny = pinf, mxx = ninf, mxy = ninf;
+#pragma unroll
+    for (int k = 0; k < COLS; ++k) {
+        const int c = k * kRegThreads + tid;
+        bx[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < n) {
+            bx[k] = gbox[c];
+            const float sx = bx[k].x + bx[k].z, sy = bx[k].y + bx[k].w;      // twice the centre: only the order matters
+            mnx = fminf(mnx, sx); mxx = fmaxf(mxx, sx);
+            mny = fminf(mny, sy); mxy = fmaxf(mxy, sy);
+        }
+        sane = sane && (area_plain(bx[k]) >= 0.f) && (fabsf(bx[k].x) + fabsf(bx[k].y) + fabsf(bx[k].z) + fabsf(bx[k].w) < 3.0e38f);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mnx = fminf(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mny = fminf(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+        mxx = fmaxf(mxx, __shfl_xor_sync(0xffffffffu, mxx, o)); mxy = fmaxf(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+    }
+    if (lane == 0) { s_red[0][warp] = mnx; s_red[1][warp] = mny; s_red[2][warp] = mxx; s_red[3][warp] = mxy; }
+    for (int i = tid; i < COLS * 256; i += kRegThreads) (&s_hist[0][0])[i] = 0;
+    for (int i = tid; i < COLS * kRegThreads; i += kRegThreads) s_perm[i] = (unsigned short)0xFFFFu;
+    for (int i = tid; i < COLS * kWarps; i += kRegThreads) {
+        const int base = i * 32;
+        s_alive[i] = n >= base + 32 ? 0xffffffffu : (n > base ? ((1u << (n - base)) - 1u) : 0u);
+    }
+    sane = __syncthreads_and(sane) && (0.f <= thr);
+    const float thr01 = (thr >= 0.f && thr <= 1.f) ? thr : 0.f;      // outside [0,1] the candidate test is plain intersection
+    mnx = s_red[0][lane]; mny = s_red[1][lane]; mxx = s_red[2][lane]; mxy = s_red[3][lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mnx = fminf(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mny = fminf(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+        mxx = fmaxf(mxx, __shfl_xor_sync(0xffffffffu, mxx, o)); mxy = fmaxf(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+    }
+    const float gsx = (mxx > mnx && (mxx - mnx) < 3.0e38f) ? 16.0f / (mxx - mnx) : 0.f;
+    const float gsy = (mxy > mny && (mxy - mny) < 3.0e38f) ? 16.0f / (mxy - mny) : 0.f;
+    // ---- counting sort of every slot's 1024 ranks by Morton key (the order inside a bucket is whatever the atomics give:
+    //      it decides which thread holds a column, nothing else)
+    unsigned kp[COLS];
+#pragma unroll
+    for (int k = 0; k < COLS; ++k) {
+        const int c = k * kRegThreads + tid;
+        kp[k] = 0u;
+        if (c < n) {
+            const int kx = min(max((int)((bx[k].x + bx[k].z - mnx) * gsx), 0), 15);
+            const int ky = min(max((int)((bx[k].y + bx[k].w - mny) * gsy), 0), 15);
+            const unsigned key = nms_part1by1_4((unsigned)kx) | (nms_part1by1_4((unsigned)ky) << 1);
+            kp[k] = (key << 16) | (unsigned)atomicAdd(&s_hist[k][key], 1);
+        }
+    }
+    __syncthreads();
+    if (warp < COLS) {      // exclusive prefix over the slot's 256 buckets: 8 per lane + a warp scan
+        int v[8], tot = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { v[j] = s_hist[warp][lane * 8 + j]; tot += v[j]; }
+        int inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        int run = inc - tot;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s_hist[warp][lane * 8 + j] = run; run += v[j]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < COLS; ++k) {
+        const int c = k * kRegThreads + tid;
+        if (c < n) s_perm[k * kRegThreads + s_hist[k][kp[k] >> 16] + (int)(kp[k] & 0xFFFFu)] = (unsigned short)tid;
+    }
+    __syncthreads();
+    // ---- pass 2: every thread takes the columns the sort dealt it; per slot the warp's bounding box of shrunken columns
+    unsigned alive = 0u;
+#pragma unroll
+    for (int k = 0; k < COLS; ++k) {
+        const unsigned r = s_perm[k * kRegThreads + tid];
+        bx[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        cl[k] = -1;
+        float4 sh = never;
+        if (r != 0xFFFFu) {
+            const int c = k * kRegThreads + (int)r;
+            bx[k] = gbox[c];
+            if (CLASS_AWARE) cl[k] = gcls[c];
+            alive |= 1u << k;
+            if (bx[k].z > bx[k].x && bx[k].w > bx[k].y) {
+                const float hx = nms_shrink_half(bx[k].x, bx[k].z, thr01), hy = nms_shrink_half(bx[k].y, bx[k].w, thr01);
+                sh = make_float4(__fadd_rn(bx[k].x, hx), __fadd_rn(bx[k].y, hy), __fsub_rn(bx[k].z, hx), __fsub_rn(bx[k].w, hy));
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            sh.x = fminf(sh.x, __shfl_xor_sync(0xffffffffu, sh.x, o)); sh.y = fminf(sh.y, __shfl_xor_sync(0xffffffffu, sh.y, o));
+            sh.z = fmaxf(sh.z, __shfl_xor_sync(0xffffffffu, sh.z, o)); sh.w = fmaxf(sh.w, __shfl_xor_sync(0xffffffffu, sh.w, o));
+        }
+        if (lane == 0) s_wbb[k][warp] = sh;
+    }
+    __syncthreads();
+
+    for (int t0 = 0; t0 < n; t0 += 64) {
+        const int tn = min(64, n - t0);
+        const int kt = t0 / kRegThreads;
+        if (tid < 64) {      // the tile's rows, by rank, from the sorted list
+            float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
+            int mc = -1;
+            if (tid < tn) {
+                mine = gbox[t0 + tid];
+                if (CLASS_AWARE) mc = gcls[t0 + tid];
+            }
+            s_tile[tid] = mine;
+            s_tarea[tid] = area_plain(mine);
+            if (CLASS_AWARE) s_tcls[tid] = mc;
+        }
+        __syncthreads();      // also: every column-pass write of the previous tile (s_alive) is done
+        // -- diagonal 64x64 bitmask tile by warp ballots: warp w handles rows w and w + 32
+        for (int r = warp; r < tn; r += kWarps) {
+            const float4 bi = s_tile[r];
+            const float ai = s_tarea[r];
+            unsigned long long bits = 0ull;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int c = h * 32 + lane;
+                bool sup = false;
+                if (c > r && c < tn) {
+                    sup = suppresses(bi, ai, s_tile[c], thr);
+                    if (CLASS_AWARE) sup = sup && (s_tcls[c] == s_tcls[r]);
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, sup);
+                bits |= (unsigned long long)m << (32 * h);
+            }
+            if (lane == 0) s_diag[r] = bits;
+        }
+        __syncthreads();
+        // -- greedy resolution of the tile by one warp (as in k_nms_suppress_reg); the rows' alive bits come from, and
+        //    go back to, the rank-indexed bitmap (nobody else touches the tile's two words now: column passes only
+        //    clear bits of ranks >= t0 + 64)
+        if (warp == 0) {
+            const unsigned w0 = s_alive[t0 >> 5], w1 = tn > 32 ? s_alive[(t0 >> 5) + 1] : 0u;
+            const unsigned long long d0 = lane < tn ? s_diag[lane] : 0ull;
+            const unsigned long long d1 = lane + 32 < tn ? s_diag[lane + 32] : 0ull;
+            unsigned long long rem = ~((unsigned long long)w0 | ((unsigned long long)w1 << 32));
+            unsigned long long kept = 0ull;
+#pragma unroll
+            for (int r = 0; r < 64; ++r) {
+                const unsigned long long dr = __shfl_sync(0xffffffffu, r < 32 ? d0 : d1, r & 31);
+                if (!((rem >> r) & 1ull)) {      // uniform across the warp
+                    kept |= 1ull << r;
+                    rem |= dr;
+                }
+            }
+            const int nk = __popcll(kept);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int r = lane + 32 * h;
+                if ((kept >> r) & 1ull) {
+                    const int pos = __popcll(kept & ((1ull << r) - 1ull));
+                    float4 v = s_tile[r];
+                    float4 sh = v;
+                    if (sane && !(v.z > v.x && v.w > v.y)) { v = never; sh = never; }
+                    else {
+                        const float hx = nms_shrink_half(v.x, v.z, thr01), hy = nms_shrink_half(v.y, v.w, thr01);
+                        sh = make_float4(__fadd_rn(v.x, hx), __fadd_rn(v.y, hy), __fsub_rn(v.z, hx), __fsub_rn(v.w, hy));
+                    }
+                    s_kbox[pos] = v;
+                    s_kshr[pos] = sh;
+                    s_karea[pos] = s_tarea[r];
+                    if (CLASS_AWARE) s_kcls[pos] = s_tcls[r];
+                }
+            }
+            if (lane == 0) {
+                s_nk = nk;
+                s_alive[t0 >> 5] = (unsigned)(~rem);
+                if (tn > 32) s_alive[(t0 >> 5) + 1] = (unsigned)((~rem) >> 32);
+            }
+        }
+        __syncthreads();
+        const int nk = s_nk;
+        if (nk == 0) continue;
+        // -- kept rows of this tile suppress every later, still-alive column
+#pragma unroll
+        for (int k = 0; k < COLS; ++k) {
+            if (k < kt) continue;                                   // the whole slot ranks before the tile
+            bool act = (alive >> k) & 1u;
+            unsigned rk = 0u;
+            if (k == kt) {                                          // the tile's own slot: only the later ranks
+                rk = s_perm[k * kRegThreads + tid];
+                act = act && (k * kRegThreads + (int)rk >= t0 + 64);
+            }
+            if (!__any_sync(0xffffffffu, act)) continue;
+            const float4 bj = bx[k];
+            bool dead = false;
+            if (sane) {
+                // which kept rows can reach any column of this warp's slot (>=, as the pair test counts a difference of +0 as a hit)
+                const float4 bb = s_wbb[k][warp];
+                const float4 r0 = s_kshr[lane & 63], r1 = s_kshr[(lane + 32) & 63];
+                const bool h0 = lane < nk && r0.z >= bb.x && bb.z >= r0.x && r0.w >= bb.y && bb.w >= r0.y;
+                const bool h1 = lane + 32 < nk && r1.z >= bb.x && bb.z >= r1.x && r1.w >= bb.y && bb.w >= r1.y;
+                const unsigned long long rows = (unsigned long long)__ballot_sync(0xffffffffu, h0) |
+                                                ((unsigned long long)__ballot_sync(0xffffffffu, h1) << 32);
+                if (rows == 0ull) continue;
+                if (act && bj.z > bj.x && bj.w > bj.y) {
+                    float thr_k = thr01;
+                    asm volatile("" : "+f"(thr_k));      // keeps the (tile-invariant) shrunken column out of registers across tiles
+                    const float hx = nms_shrink_half(bj.x, bj.z, thr_k), hy = nms_shrink_half(bj.y, bj.w, thr_k);
+                    const float jx = __fadd_rn(bj.x, hx), jy = __fadd_rn(bj.y, hy), jz = __fsub_rn(bj.z, hx), jw = __fsub_rn(bj.w, hy);
+                    const float aj = area_plain(bj);
+                    unsigned long long m = rows;
+                    while (m && !dead) {
+                        const int q = __ffsll((long long)m) - 1;
+                        m &= m - 1ull;
+                        const float4 bi = s_kshr[q];
+                        // a > b  <=>  fl(a - b) > 0: four FADD sign bits (see k_nms_suppress_reg); +0 reads as a hit
+                        const int sg = __float_as_int(__fsub_rn(bi.z, jx)) | __float_as_int(__fsub_rn(jz, bi.x)) |
+                                       __float_as_int(__fsub_rn(bi.w, jy)) | __float_as_int(__fsub_rn(jw, bi.y));
+                        if (sg >= 0) {
+                            if (CLASS_AWARE && s_kcls[q] != cl[k]) continue;
+                            const float iou = iou_nms(s_kbox[q], s_karea[q], bj, aj);
+                            dead = !(iou <= thr);
+                        }
+                    }
+                }
+            } else if (act) {
+                const float aj = area_plain(bj);
+                (void)aj;
+                for (int q = 0; q < nk && !dead; ++q) {
+                    if (CLASS_AWARE && s_kcls[q] != cl[k]) continue;
+                    dead = suppresses(s_kbox[q], s_karea[q], bj, thr);
+                }
+            }
+            if (dead) {
+                alive &= ~(1u << k);
+                if (k != kt) rk = s_perm[k * kRegThreads + tid];
+                const int rank = k * kRegThreads + (int)rk;
+                atomicAnd(&s_alive[rank >> 5], ~(1u << (rank & 31)));
+            }
+        }
+        // no barrier here: the next tile's first barrier orders these reads of s_k* before warp 0 rewrites them
+    }
+
+    // -- survivors: the rank-indexed bitmap, compacted by one warp (ballot prefix)
+    __syncthreads();
+    if (warp == 0) {
+        int base = 0;
+        for (int c0 = 0; c0 < n; c0 += 32) {
+            const int c = c0 + lane;
+            const bool al = c < n && ((s_alive[c >> 5] >> (c & 31)) & 1u);
+            const unsigned m = __ballot_sync(0xffffffffu, al);
+            if (al) {
+                const size_t o = (size_t)b * A + base + __popc(m & ((1u << lane) - 1u));
+                const size_t s = (size_t)b * A + c;
+                if (keep_anchor) keep_anchor[o] = sanchor[s];
+                if (keep_boxes) {
+                    const float4 v = sbox[s];
+                    // boxes / img_size, clamp to [0,1]  (train_yolo11_cuda.py:347-350)
+                    float4 q = make_float4(YS_DIV(v.x, img_size), YS_DIV(v.y, img_size), YS_DIV(v.z, img_size), YS_DIV(v.w, img_size));
+                    q.x = fminf2(fmaxf2(q.x, 0.f), 1.f); q.y = fminf2(fmaxf2(q.y, 0.f), 1.f);
+                    q.z = fminf2(fmaxf2(q.z, 0.f), 1.f); q.w = fminf2(fmaxf2(q.w, 0.f), 1.f);
+                    keep_boxes[o] = q;
+                }
+                if (keep_scores) keep_scores[o] = sscore[s];
+                if (keep_labels) keep_labels[o] = scls[s];
+            }
+            base += __popc(m);
+        }
+        if (lane == 0) keep_count[b] = base;
+    }
+}
+
 struct NmsWorkspace {
     unsigned long long *keys;
     float4 *boxes, *sbox;
@@ -607,8 +932,16 @@ static int run_sort_suppress(const NmsWorkspace &W, int B, int A, float iou_thr,
     k_nms_sort<<<B, kSortThreads, sort_smem, stream>>>(W.keys, W.count, A, boxes, cls, W.sbox, W.sscore, W.scls, W.sanchor);
     YS_CHECK_LAUNCH("k_nms_sort");
     if (A <= 9 * kRegThreads) {      // register-resident columns (every 640 px / 8400-candidate case)
+#ifndef YS_NMS_ZORDER
+#define YS_NMS_ZORDER 1      // 0: k_nms_suppress_reg (columns in rank order), kept for A/B
+#endif
+#if YS_NMS_ZORDER
+#define YS_NMS_REG_KERNEL k_nms_suppress_zreg
+#else
+#define YS_NMS_REG_KERNEL k_nms_suppress_reg
+#endif
 #define YS_LAUNCH_REG(CA, COLS)                                                                                              \
-    k_nms_suppress_reg<CA, COLS><<<B, kRegThreads, 0, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr,      \
+    YS_NMS_REG_KERNEL<CA, COLS><<<B, kRegThreads, 0, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr,      \
                                                                 img_size, keep_anchor, (float4 *)keep_boxes, keep_scores,     \
                                                                 keep_labels, keep_count)
         if (A <= 2 * kRegThreads) { if (class_aware) YS_LAUNCH_REG(true, 2); else YS_LAUNCH_REG(false, 2); }
