@@ -565,10 +565,10 @@ k_nms_suppress_reg(const int *__restrict__ count, int A, const float4 *__restric
 }
 
 // ---------------------------------------------------------------------------------------------------
-// k_nms_suppress_zreg: k_nms_suppress_reg with the columns handed to the threads in Z-ORDER of their centres.
+// k_nms_suppress_zreg: k_nms_suppress_reg with the columns handed to the threads along a HILBERT CURVE over their centres.
 // In k_nms_suppress_reg thread t owns the score ranks t, t+1024, ...: the 32 columns a warp holds in one slot are
 // scattered over the image and every column meets every kept row of a tile (N^2/2 pair tests, ~8 instructions
-// each).  Here the 1024 ranks of a slot are dealt out by a counting sort on the 8-bit Morton key of the box centre
+// each).  Here the 1024 ranks of a slot are dealt out by a counting sort on the 8-bit Hilbert index of the box centre
 // (16 x 16 grid over the image's own extent), so a warp's 32 columns of a slot are neighbours; the warp keeps the
 // bounding box of its (shrunken, see nms_shrink_half) columns per slot, and per tile and slot ONE warp-wide test
 // (two rows per lane, two ballots) picks the kept rows that can reach any of them -- the pair loop runs over those
@@ -579,11 +579,20 @@ k_nms_suppress_reg(const int *__restrict__ count, int A, const float4 *__restric
 // tile's boxes are read from the sorted list in global memory (1 KB per tile, L2), and s_perm[slot][thread] gives
 // the rank a thread's column has inside the slot (needed only in the slot the current tile lies in).
 // ---------------------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned nms_part1by1_4(unsigned v) {
-    v &= 0xFu;
-    v = (v | (v << 2)) & 0x33u;
-    v = (v | (v << 1)) & 0x55u;
-    return v;
+// Hilbert index of cell (x, y) in a 16 x 16 grid (0..255): consecutive indices are always edge neighbours, so a run of
+// cells never jumps across the image the way a Morton run does at quadrant borders.
+__device__ __forceinline__ unsigned nms_hilbert16(int x, int y) {
+    unsigned d = 0u;
+#pragma unroll
+    for (int s = 8; s > 0; s >>= 1) {
+        const int rx = (x & s) ? 1 : 0, ry = (y & s) ? 1 : 0;
+        d += (unsigned)(s * s * ((3 * rx) ^ ry));
+        if (ry == 0) {
+            if (rx == 1) { x = 15 - x; y = 15 - y; }
+            const int t = x; x = y; y = t;
+        }
+    }
+    return d;
 }
 
 template <bool CLASS_AWARE, int COLS>
@@ -657,7 +666,7 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
     }
     const float gsx = (mxx > mnx && (mxx - mnx) < 3.0e38f) ? 16.0f / (mxx - mnx) : 0.f;
     const float gsy = (mxy > mny && (mxy - mny) < 3.0e38f) ? 16.0f / (mxy - mny) : 0.f;
-    // ---- counting sort of every slot's 1024 ranks by Morton key (the order inside a bucket is whatever the atomics give:
+    // ---- counting sort of every slot's 1024 ranks by Hilbert index (the order inside a bucket is whatever the atomics give:
     //      it decides which thread holds a column, nothing else)
     unsigned kp[COLS];
 #pragma unroll
@@ -667,7 +676,7 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
         if (c < n) {
             const int kx = min(max((int)((bx[k].x + bx[k].z - mnx) * gsx), 0), 15);
             const int ky = min(max((int)((bx[k].y + bx[k].w - mny) * gsy), 0), 15);
-            const unsigned key = nms_part1by1_4((unsigned)kx) | (nms_part1by1_4((unsigned)ky) << 1);
+            const unsigned key = nms_hilbert16(kx, ky);
             kp[k] = (key << 16) | (unsigned)atomicAdd(&s_hist[k][key], 1);
         }
     }
@@ -720,19 +729,21 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
     }
     __syncthreads();
 
+    // the tile's rows come by rank from the sorted list in global memory; the next tile's are fetched before the column
+    // pass of the current one, so their L2 latency is off the serial part of the tile
+    float4 pre = make_float4(0.f, 0.f, 0.f, 0.f);
+    int prec = -1;
+    if (tid < 64 && tid < n) {
+        pre = gbox[tid];
+        if (CLASS_AWARE) prec = gcls[tid];
+    }
     for (int t0 = 0; t0 < n; t0 += 64) {
         const int tn = min(64, n - t0);
         const int kt = t0 / kRegThreads;
-        if (tid < 64) {      // the tile's rows, by rank, from the sorted list
-            float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
-            int mc = -1;
-            if (tid < tn) {
-                mine = gbox[t0 + tid];
-                if (CLASS_AWARE) mc = gcls[t0 + tid];
-            }
-            s_tile[tid] = mine;
-            s_tarea[tid] = area_plain(mine);
-            if (CLASS_AWARE) s_tcls[tid] = mc;
+        if (tid < 64) {
+            s_tile[tid] = pre;
+            s_tarea[tid] = area_plain(pre);
+            if (CLASS_AWARE) s_tcls[tid] = prec;
         }
         __syncthreads();      // also: every column-pass write of the previous tile (s_alive) is done
         // -- diagonal 64x64 bitmask tile by warp ballots: warp w handles rows w and w + 32
@@ -798,6 +809,14 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
         }
         __syncthreads();
         const int nk = s_nk;
+        if (tid < 64) {
+            pre = make_float4(0.f, 0.f, 0.f, 0.f);
+            prec = -1;
+            if (t0 + 64 + tid < n) {
+                pre = gbox[t0 + 64 + tid];
+                if (CLASS_AWARE) prec = gcls[t0 + 64 + tid];
+            }
+        }
         if (nk == 0) continue;
         // -- kept rows of this tile suppress every later, still-alive column
 #pragma unroll
