@@ -846,18 +846,22 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
                     const float hx = nms_shrink_half(bj.x, bj.z, thr_k), hy = nms_shrink_half(bj.y, bj.w, thr_k);
                     const float jx = __fadd_rn(bj.x, hx), jy = __fadd_rn(bj.y, hy), jz = __fsub_rn(bj.z, hx), jw = __fsub_rn(bj.w, hy);
                     const float aj = area_plain(bj);
-                    unsigned long long m = rows;
-                    while (m && !dead) {
-                        const int q = __ffsll((long long)m) - 1;
-                        m &= m - 1ull;
-                        const float4 bi = s_kshr[q];
-                        // a > b  <=>  fl(a - b) > 0: four FADD sign bits (see k_nms_suppress_reg); +0 reads as a hit
-                        const int sg = __float_as_int(__fsub_rn(bi.z, jx)) | __float_as_int(__fsub_rn(jz, bi.x)) |
-                                       __float_as_int(__fsub_rn(bi.w, jy)) | __float_as_int(__fsub_rn(jw, bi.y));
-                        if (sg >= 0) {
-                            if (CLASS_AWARE && s_kcls[q] != cl[k]) continue;
-                            const float iou = iou_nms(s_kbox[q], s_karea[q], bj, aj);
-                            dead = !(iou <= thr);
+                    // the surviving rows, 32 at a time (32-bit find-first-set / clear-lowest: half the loop overhead of 64-bit)
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        unsigned m = (unsigned)(rows >> (32 * h));
+                        while (m && !dead) {
+                            const int q = __ffs((int)m) - 1 + 32 * h;
+                            m &= m - 1u;
+                            const float4 bi = s_kshr[q];
+                            // a > b  <=>  fl(a - b) > 0: four FADD sign bits (see k_nms_suppress_reg); +0 reads as a hit
+                            const int sg = __float_as_int(__fsub_rn(bi.z, jx)) | __float_as_int(__fsub_rn(jz, bi.x)) |
+                                           __float_as_int(__fsub_rn(bi.w, jy)) | __float_as_int(__fsub_rn(jw, bi.y));
+                            if (sg >= 0) {
+                                if (CLASS_AWARE && s_kcls[q] != cl[k]) continue;
+                                const float iou = iou_nms(s_kbox[q], s_karea[q], bj, aj);
+                                dead = !(iou <= thr);
+                            }
                         }
                     }
                 }
@@ -879,32 +883,46 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
         // no barrier here: the next tile's first barrier orders these reads of s_k* before warp 0 rewrites them
     }
 
-    // -- survivors: the rank-indexed bitmap, compacted by one warp (ballot prefix)
+    // -- survivors: the rank-indexed bitmap.  One warp turns the per-word popcounts into output offsets, then ALL warps
+    //    write the kept detections (one 32-rank word per warp and trip; a single warp walking 8400 ranks with four
+    //    dependent global loads per trip was 15 % of the kernel)
     __syncthreads();
+    int *s_base = &s_hist[0][0];                                   // the sort's histogram is free now
+    const int nwords = (n + 31) >> 5;
     if (warp == 0) {
-        int base = 0;
-        for (int c0 = 0; c0 < n; c0 += 32) {
-            const int c = c0 + lane;
-            const bool al = c < n && ((s_alive[c >> 5] >> (c & 31)) & 1u);
-            const unsigned m = __ballot_sync(0xffffffffu, al);
-            if (al) {
-                const size_t o = (size_t)b * A + base + __popc(m & ((1u << lane) - 1u));
-                const size_t s = (size_t)b * A + c;
-                if (keep_anchor) keep_anchor[o] = sanchor[s];
-                if (keep_boxes) {
-                    const float4 v = sbox[s];
-                    // boxes / img_size, clamp to [0,1]  (train_yolo11_cuda.py:347-350)
-                    float4 q = make_float4(YS_DIV(v.x, img_size), YS_DIV(v.y, img_size), YS_DIV(v.z, img_size), YS_DIV(v.w, img_size));
-                    q.x = fminf2(fmaxf2(q.x, 0.f), 1.f); q.y = fminf2(fmaxf2(q.y, 0.f), 1.f);
-                    q.z = fminf2(fmaxf2(q.z, 0.f), 1.f); q.w = fminf2(fmaxf2(q.w, 0.f), 1.f);
-                    keep_boxes[o] = q;
-                }
-                if (keep_scores) keep_scores[o] = sscore[s];
-                if (keep_labels) keep_labels[o] = scls[s];
+        int running = 0;
+        for (int w0 = 0; w0 < nwords; w0 += 32) {
+            const int w = w0 + lane;
+            const int cnt = w < nwords ? __popc(s_alive[w]) : 0;
+            int inc = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
             }
-            base += __popc(m);
+            if (w < nwords) s_base[w] = running + inc - cnt;
+            running += __shfl_sync(0xffffffffu, inc, 31);
         }
-        if (lane == 0) keep_count[b] = base;
+        if (lane == 0) keep_count[b] = running;
+    }
+    __syncthreads();
+    for (int w = warp; w < nwords; w += kWarps) {
+        const unsigned m = s_alive[w];                             // bits of ranks >= n are zero
+        if ((m >> lane) & 1u) {
+            const size_t o = (size_t)b * A + s_base[w] + __popc(m & ((1u << lane) - 1u));
+            const size_t s = (size_t)b * A + w * 32 + lane;
+            if (keep_anchor) keep_anchor[o] = sanchor[s];
+            if (keep_boxes) {
+                const float4 v = sbox[s];
+                // boxes / img_size, clamp to [0,1]  (train_yolo11_cuda.py:347-350)
+                float4 q = make_float4(YS_DIV(v.x, img_size), YS_DIV(v.y, img_size), YS_DIV(v.z, img_size), YS_DIV(v.w, img_size));
+                q.x = fminf2(fmaxf2(q.x, 0.f), 1.f); q.y = fminf2(fmaxf2(q.y, 0.f), 1.f);
+                q.z = fminf2(fmaxf2(q.z, 0.f), 1.f); q.w = fminf2(fmaxf2(q.w, 0.f), 1.f);
+                keep_boxes[o] = q;
+            }
+            if (keep_scores) keep_scores[o] = sscore[s];
+            if (keep_labels) keep_labels[o] = scls[s];
+        }
     }
 }
 
