@@ -129,3 +129,74 @@ def test_nms_full_batch_256_properties(cuda_lib):
         iou = calculate_iou_batch(bx, bx)
         iou.fill_diagonal_(0)
         assert (iou <= 0.7).all()
+
+
+def _adversarial_boxes(n, seed, scale=1.0, offset=0.0):
+    """Geometry that stresses the candidate filters of the suppress kernels: lattice boxes sharing edges (differences
+    of exactly +0), duplicates, zero-width / zero-height / zero-area boxes, contained boxes whose IoU sits at the
+    threshold (i inside j, same height, width = thr * W * (1 + d) for tiny d), shifted copies, tiny boxes."""
+    g = torch.Generator().manual_seed(seed)
+    cell = 16.0
+    ij = torch.randint(0, 24, (n, 2), generator=g).float()
+    wh = torch.randint(1, 4, (n, 2), generator=g).float()
+    boxes = torch.cat((ij * cell, (ij + wh) * cell), 1)                      # lattice: shared edges everywhere
+    k = n // 8
+    boxes[k:2 * k] = boxes[:k]                                                # exact duplicates
+    boxes[2 * k:3 * k, 2] = boxes[2 * k:3 * k, 0]                             # zero width
+    boxes[3 * k:4 * k, 3] = boxes[3 * k:4 * k, 1]                             # zero height
+    for thr, lo in ((0.7, 4 * k), (0.3, 5 * k)):                              # IoU at the threshold, both sides of it
+        base = boxes[:k].clone()
+        W = base[:, 2] - base[:, 0]
+        d = (torch.rand(k, generator=g) - 0.5) * 2e-4
+        a = torch.rand(k, generator=g) * (1 - thr) * 0.5 * W
+        inner = base.clone()
+        inner[:, 0] = base[:, 0] + a
+        inner[:, 2] = inner[:, 0] + thr * W * (1 + d)
+        boxes[lo:lo + k] = inner
+    sh = boxes[:k].clone()                                                    # copies shifted along y: IoU = ih / (2h - ih)
+    H = sh[:, 3] - sh[:, 1]
+    sh[:, 1] += H * torch.rand(k, generator=g) * 0.4
+    sh[:, 3] = sh[:, 1] + H
+    boxes[6 * k:7 * k] = sh
+    tiny = boxes[7 * k:].clone()                                              # tiny boxes, some nested in each other
+    tiny[:, 2:] = tiny[:, :2] + torch.rand(tiny.shape[0], 2, generator=g) * 1e-3
+    boxes[7 * k:] = tiny
+    boxes = boxes * scale + offset
+    scores = torch.rand(n, generator=g)
+    scores[::7] = scores[3]                                                   # ties -> lower index first
+    perm = torch.randperm(n, generator=g)
+    return boxes[perm].contiguous(), scores[perm].contiguous()
+
+
+@pytest.mark.parametrize("n,seed,scale,offset", [(3000, 340, 1.0, 0.0), (9000, 341, 1.0, 0.0), (4000, 342, 1.0, 30000.0),
+                                                 (2500, 343, 1e-3, 0.0), (6000, 344, 2.5e4, -3e6)])
+def test_nms_adversarial_geometry_vs_c_oracle(cuda_lib, n, seed, scale, offset):
+    """Keep lists bit-exact against the C oracle on geometry built to break a conservative candidate filter (touching
+    edges, degenerate boxes, IoU within 1e-4 of the threshold, tiny boxes far from the origin where one ulp of a
+    coordinate is larger than the box), at thresholds on, inside and outside [0, 1]; 3000..9000 boxes cover the
+    5- and 9-column instantiations."""
+    from oracle import c_oracle
+    from yolo_scratch_b200.train_yolo11_cuda import nms_simple
+    boxes, scores = _adversarial_boxes(n, seed, scale, offset)
+    for thr in (0.7, 0.3, 0.0, 0.999, 1.0, 1.5):
+        keep = nms_simple(boxes.cuda(), scores.cuda(), thr)
+        assert keep == c_oracle.nms(boxes, scores, thr), (n, thr)
+    cls = (torch.arange(n) % 3).int()
+    keep = nms_simple(boxes.cuda(), scores.cuda(), 0.5, labels=cls.cuda())
+    assert keep == c_oracle.nms(boxes, scores, 0.5, labels=cls.numpy())
+
+
+def test_nms_non_finite_and_inverted_boxes_vs_c_oracle(cuda_lib):
+    """Boxes with x2 < x1, infinities and NaN take the kernels' exact (unfiltered) path; the keep list still equals the
+    oracle's, which applies the reference's `ious <= thr` literally (a NaN IoU drops the box, train_yolo11_cuda.py:396)."""
+    from oracle import c_oracle
+    from yolo_scratch_b200.train_yolo11_cuda import nms_simple
+    boxes, scores = _adversarial_boxes(3000, 350)
+    boxes[5] = torch.tensor([50.0, 50.0, 10.0, 90.0])
+    boxes[6] = torch.tensor([50.0, 90.0, 90.0, 10.0])
+    keep = nms_simple(boxes.cuda(), scores.cuda(), 0.5)
+    assert keep == c_oracle.nms(boxes, scores, 0.5)
+    boxes[77] = torch.tensor([0.0, 0.0, float("inf"), 10.0])
+    boxes[78] = torch.tensor([float("nan"), 0.0, 5.0, 10.0])
+    keep = nms_simple(boxes.cuda(), scores.cuda(), 0.5)
+    assert keep == c_oracle.nms(boxes, scores, 0.5)
