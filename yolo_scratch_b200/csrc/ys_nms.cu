@@ -773,15 +773,17 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
             const unsigned long long d0 = lane < tn ? s_diag[lane] : 0ull;
             const unsigned long long d1 = lane + 32 < tn ? s_diag[lane + 32] : 0ull;
             unsigned long long rem = ~((unsigned long long)w0 | ((unsigned long long)w1 << 32));
-            unsigned long long kept = 0ull;
-#pragma unroll
-            for (int r = 0; r < 64; ++r) {
+            // only rows that suppress something inside the tile need a turn (in rank order); a row is kept iff its bit of
+            // `rem` is clear at its turn, and later rows only set bits above themselves, so kept = ~rem at the end
+            unsigned long long nz = (unsigned long long)__ballot_sync(0xffffffffu, d0 != 0ull) |
+                                    ((unsigned long long)__ballot_sync(0xffffffffu, d1 != 0ull) << 32);
+            while (nz) {
+                const int r = __ffsll((long long)nz) - 1;
+                nz &= nz - 1ull;
                 const unsigned long long dr = __shfl_sync(0xffffffffu, r < 32 ? d0 : d1, r & 31);
-                if (!((rem >> r) & 1ull)) {      // uniform across the warp
-                    kept |= 1ull << r;
-                    rem |= dr;
-                }
+                if (!((rem >> r) & 1ull)) rem |= dr;      // uniform across the warp
             }
+            const unsigned long long kept = ~rem;
             const int nk = __popcll(kept);
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
