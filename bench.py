@@ -350,7 +350,8 @@ def bench_nms(dev, lib, B=256, reps=5):
     return {"workload": "configs[3]: B=256, 8400 candidates x 80 classes, conf 0.001 / IoU 0.7, class-agnostic",
             "images_per_s": B / (ms * 1e-3), "ms": ms, "kept_per_image": kept,
             "algorithmic_gbs": alg / (ms * 1e-3) / 1e9, "approx_pair_tests_per_s": pairs / (ms * 1e-3),
-            "note": "pair-rate (fp32 ALU) bound, not HBM bound (SURVEY §8d caveat)"}
+            "note": "not HBM bound (SURVEY §8d caveat): greedy tile chain, barrier/latency bound after the spatial culling of "
+                    "pair tests (DESIGN.md §4 NMS); pair figure = kept rows x later columns the reference would test"}
 
 
 def main():
