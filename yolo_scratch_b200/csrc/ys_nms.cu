@@ -702,11 +702,14 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
         if (c < n) s_perm[k * kRegThreads + s_hist[k][kp[k] >> 16] + (int)(kp[k] & 0xFFFFu)] = (unsigned short)tid;
     }
     __syncthreads();
-    // ---- pass 2: every thread takes the columns the sort dealt it; per slot the warp's bounding box of shrunken columns
+    // ---- pass 2: every thread takes the columns the sort dealt it; per slot the warp's bounding box of shrunken columns.
+    //      Slot k is dealt ROTATED by 7*k warps: dealt straight, the nine slots of a warp would all lie at the same place
+    //      along the curve, one region of the image, and a tile whose kept rows cluster there would load that warp nine
+    //      times over while the others wait at the tile's barrier; rotated, a warp's slots sample nine regions.
     unsigned alive = 0u;
 #pragma unroll
     for (int k = 0; k < COLS; ++k) {
-        const unsigned r = s_perm[k * kRegThreads + tid];
+        const unsigned r = s_perm[k * kRegThreads + ((tid + k * 7 * 32) & (kRegThreads - 1))];
         bx[k] = make_float4(0.f, 0.f, 0.f, 0.f);
         cl[k] = -1;
         float4 sh = never;
@@ -827,7 +830,7 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
             bool act = (alive >> k) & 1u;
             unsigned rk = 0u;
             if (k == kt) {                                          // the tile's own slot: only the later ranks
-                rk = s_perm[k * kRegThreads + tid];
+                rk = s_perm[k * kRegThreads + ((tid + k * 7 * 32) & (kRegThreads - 1))];
                 act = act && (k * kRegThreads + (int)rk >= t0 + 64);
             }
             if (!__any_sync(0xffffffffu, act)) continue;
@@ -877,7 +880,7 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
             }
             if (dead) {
                 alive &= ~(1u << k);
-                if (k != kt) rk = s_perm[k * kRegThreads + tid];
+                if (k != kt) rk = s_perm[k * kRegThreads + ((tid + k * 7 * 32) & (kRegThreads - 1))];
                 const int rank = k * kRegThreads + (int)rk;
                 atomicAnd(&s_alive[rank >> 5], ~(1u << (rank & 31)));
             }
