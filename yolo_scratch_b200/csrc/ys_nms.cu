@@ -642,7 +642,7 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
             mnx = fminf(mnx, sx); mxx = fmaxf(mxx, sx);
             mny = fminf(mny, sy); mxy = fmaxf(mxy, sy);
         }
-        sane = sane && (area_plain(bx[k]) >= 0.f) && (fabsf(bx[k].x) + fabsf(bx[k].y) + fabsf(bx[k].z) + fabsf(bx[k].w) < 3.0e38f);
+        sane = sane && (area_plain(bx[k]) >= 0.f) && (area_plain(bx[k]) < 1.0e38f) && (fabsf(bx[k].x) + fabsf(bx[k].y) + fabsf(bx[k].z) + fabsf(bx[k].w) < 3.0e38f);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -864,8 +864,13 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
                                            __float_as_int(__fsub_rn(bi.w, jy)) | __float_as_int(__fsub_rn(jw, bi.y));
                             if (sg >= 0) {
                                 if (CLASS_AWARE && s_kcls[q] != cl[k]) continue;
-                                const float iou = iou_nms(s_kbox[q], s_karea[q], bj, aj);
-                                dead = !(iou <= thr);
+                                // iou_nms, with the division taken only when the quotient could exceed thr: in the sane case
+                                // (finite areas < 1e38, so nothing overflows) den > 0 and fl(inter / den) <= (inter / den) * (1 + 2^-24),
+                                // hence inter <= 0.999 * thr * den  =>  IoU < thr.  Most candidates end here.
+                                const float4 kb = s_kbox[q];
+                                const float inter = inter_area(kb.x, kb.y, kb.z, kb.w, bj.x, bj.y, bj.z, bj.w);
+                                const float den = YS_ADD(YS_SUB(YS_ADD(s_karea[q], aj), inter), kEpsNms);
+                                if (inter > __fmul_rn(0.999f * thr, den)) dead = !(YS_DIV(inter, den) <= thr);
                             }
                         }
                     }
