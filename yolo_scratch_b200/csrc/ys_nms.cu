@@ -130,8 +130,30 @@ __global__ void k_nms_keys_single(const float *__restrict__ scores, int N, unsig
 }
 
 // ---------------------------------------------------------------------------------------------------
-// sort: descending bitonic sort of count[b] keys padded with zeros to a power of two.
+// sort: descending order of count[b] keys (unique: score bits << 32 | ~anchor) in shared memory.
+// A bitonic network needs a power-of-two length, and 8400 candidates would mean 16384 slots, half of them padding
+// (105 stages of 8 compare-exchanges per thread).  Instead the keys are split at H = the largest power of two <= n:
+// the first H are sorted by one network, the remaining n - H (padded to their own power of two) by a second, small
+// one, and every key then finds its final position by one binary search in the OTHER run (own index + number of
+// larger keys there) and is gathered straight to its place in the sorted outputs: 8192 + 256 slots instead of 16384
+// at n = 8400.
 // ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void nms_bitonic_desc(unsigned long long *s, int P) {      // whole block; ends on a barrier
+    for (int k = 2; k <= P; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < (P >> 1); t += kSortThreads) {
+                // t-th compare-exchange of this stage
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const int p = i | j;
+                const bool desc = ((i & k) == 0);
+                const unsigned long long x = s[i], y = s[p];
+                if ((x < y) == desc) { s[i] = y; s[p] = x; }
+            }
+            __syncthreads();
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kSortThreads)
 k_nms_sort(const unsigned long long *__restrict__ keys, const int *__restrict__ count, int A,
            const float4 *__restrict__ boxes, const int *__restrict__ cls, float4 *__restrict__ sbox,
@@ -140,28 +162,29 @@ k_nms_sort(const unsigned long long *__restrict__ keys, const int *__restrict__ 
     const int b = blockIdx.x;
     const int n = count[b];
     if (n == 0) return;
-    int P = 1;
-    while (P < n) P <<= 1;
+    int H = 1;
+    while (H * 2 <= n) H <<= 1;                  // largest power of two <= n
+    const int nb = n - H;                        // keys of the second run
+    int P2 = 0;
+    if (nb > 0) { P2 = 1; while (P2 < nb) P2 <<= 1; }
+    unsigned long long *run_a = s_keys, *run_b = s_keys + H;      // H + P2 <= the power of two >= n the host sized for
     const unsigned long long *src = keys + (size_t)b * A;
-    for (int i = threadIdx.x; i < P; i += kSortThreads) s_keys[i] = i < n ? src[i] : 0ull;
+    for (int i = threadIdx.x; i < H + P2; i += kSortThreads) s_keys[i] = i < n ? src[i] : 0ull;      // real keys are never 0
     __syncthreads();
-    for (int k = 2; k <= P; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = threadIdx.x; t < (P >> 1); t += kSortThreads) {
-                // t-th compare-exchange of this stage
-                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-                const int p = i | j;
-                const bool desc = ((i & k) == 0);
-                const unsigned long long x = s_keys[i], y = s_keys[p];
-                if ((x < y) == desc) { s_keys[i] = y; s_keys[p] = x; }
-            }
-            __syncthreads();
-        }
-    }
+    nms_bitonic_desc(run_a, H);
+    if (P2 > 1) nms_bitonic_desc(run_b, P2);
     for (int r = threadIdx.x; r < n; r += kSortThreads) {
         const unsigned long long key = s_keys[r];
+        // how many keys of the other run are larger (both runs descend; keys are unique)
+        const unsigned long long *other = r < H ? run_b : run_a;
+        int lo = 0, hi = r < H ? nb : H;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (other[mid] > key) lo = mid + 1; else hi = mid;
+        }
+        const int pos = (r < H ? r : r - H) + lo;
         const int a = (int)(0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull));
-        const size_t o = (size_t)b * A + r;
+        const size_t o = (size_t)b * A + pos;
         sbox[o] = boxes[(size_t)b * A + a];
         sscore[o] = score_from_ordered((unsigned)(key >> 32));
         scls[o] = cls ? cls[(size_t)b * A + a] : 0;
