@@ -69,7 +69,6 @@ int ys_device_info(int *sm_count, int *cc_major, int *cc_minor);
 #define YS_STAGE_ASSIGN 2 /* k_assign   decode + scan + forced-assignment fix-up + target_scores_sum */
 #define YS_STAGE_LOSS 4   /* k_loss     BCE + CIoU + DFL forward and backward + ordered final reduction */
 #define YS_STAGE_ALL 7
-#define YS_STAGE_DIAG_LEGACY_LOSS 512 /* A/B only: run the non-persistent k_loss instead of k_loss_stream (same results) */
 #define YS_STAGE_DIAG_NOFIXUP 256 /* profiling only: k_assign skips the forced-assignment fix-up (results then differ) */
 size_t ys_detection_loss_workspace_bytes(int B, int A, int n_gt, int nc);
 int ys_detection_loss(int n_levels, const float *const *level_x_host, float *const *level_grad_host,
@@ -152,6 +151,22 @@ int ys_pairwise_iou(const float *boxes1, int N, const float *boxes2, int M, int 
  * gout may be NULL (= ones). */
 int ys_bbox_iou(const float *box1, const float *box2, int n, int xywh, int mode, float eps, float *out,
                 const float *gout, float *grad_box1, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * BboxLoss.forward with _df_loss and bbox2dist (losses/yolo_v8_loss.py:280-310, :312-324, :327-330) on dense,
+ * already-assigned tensors (stand-alone use; ys_detection_loss fuses the same arithmetic into its own kernels).
+ *  pred_dist (n, 4*reg_max) logits, pred_bboxes (n,4) xyxy and target_bboxes (n,4) xyxy in grid units,
+ *  anchor_points (A,2) grid units with n = B*A (row i uses anchor i % A), target_scores (n, nc),
+ *  fg_mask (n) u8, target_scores_sum: DEVICE scalar.
+ *  loss_out[2] = {loss_iou, loss_dfl} (loss_dfl = 0 when reg_max == 1, :307-308).
+ *  grad_pred_bboxes (n,4) = d loss_iou / d pred_bboxes and grad_pred_dist (n, 4*reg_max) = d loss_dfl / d pred_dist
+ *  (zero rows for background); either may be NULL.
+ */
+size_t ys_bbox_loss_workspace_bytes(int n);
+int ys_bbox_loss(const float *pred_dist, const float *pred_bboxes, const float *anchor_points,
+                 const float *target_bboxes, const float *target_scores, const uint8_t *fg_mask,
+                 const float *target_scores_sum, int n, int A, int nc, int reg_max, float *loss_out,
+                 float *grad_pred_bboxes, float *grad_pred_dist, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ---------------------------------------------------------------------------
  * Greedy detection-to-GT matching of evaluate_detections (utils/metrics.py:147-205, :211-256): per image,

@@ -219,13 +219,41 @@ def ltrb_to_xyxy(ltrb: torch.Tensor, anchor_points: torch.Tensor) -> torch.Tenso
 
 
 # ----------------------------------------------------------------------------
+# a12  BboxLoss.forward + _df_loss + bbox2dist    losses/yolo_v8_loss.py:280-330
+# ----------------------------------------------------------------------------
+def bbox_loss(pred_dist, pred_bboxes, anchor_points, target_bboxes, target_scores, target_scores_sum, fg_mask,
+              reg_max: int):
+    """Stand-alone BboxLoss.forward on dense tensors -> (loss_iou, loss_dfl); autograd attached to
+    pred_dist / pred_bboxes.  Boxes in grid units."""
+    fgb = fg_mask.bool()
+    w = target_scores.sum(-1)[fgb].unsqueeze(-1)                                   # :297
+    ciou = pair_iou_xyxy(pred_bboxes[fgb], target_bboxes[fgb], ciou=True)          # :298
+    loss_iou = ((1.0 - ciou) * w).sum() / target_scores_sum                        # :299
+    if reg_max <= 1:
+        return loss_iou, torch.tensor(0.0)                                         # :307-308
+    x1y1, x2y2 = target_bboxes.chunk(2, -1)
+    hi_clamp = reg_max - 1 - 0.01
+    tgt = torch.cat((anchor_points - x1y1, x2y2 - anchor_points), -1).clamp(0, hi_clamp)[fgb]   # :303, :327-330, :314
+    lo = tgt.long()
+    w_lo = (lo + 1) - tgt
+    logits = pred_dist[fgb].view(-1, reg_max)
+    ce_lo = F.cross_entropy(logits, lo.view(-1), reduction="none").view(lo.shape) * w_lo          # :320
+    ce_hi = F.cross_entropy(logits, (lo + 1).view(-1), reduction="none").view(lo.shape) * (1 - w_lo)   # :321
+    loss_dfl = ((ce_lo + ce_hi).mean(-1, keepdim=True) * w).sum() / target_scores_sum               # :304-305, :323
+    return loss_iou, loss_dfl
+
+
+# ----------------------------------------------------------------------------
 # a1, a11, a12  v8DetectionLoss.__call__          losses/yolo_v8_loss.py:372-499
 # ----------------------------------------------------------------------------
 def detection_loss(feats: Sequence[torch.Tensor], batch: Dict[str, torch.Tensor], nc: int, reg_max: int,
                    strides: Sequence[float], hyp=(7.5, 0.5, 1.5), alpha: float = 0.5, beta: float = 4.0,
-                   return_parts: bool = False):
+                   return_parts: bool = False, assign_boxes_px: torch.Tensor = None):
     """Returns (loss.sum()*B, loss_items.detach()) with autograd attached to `feats`.
-    With return_parts also a dict of the intermediate assignment tensors."""
+    With return_parts also a dict of the intermediate assignment tensors.
+    assign_boxes_px (B, A, 4): "spliced" mode of SURVEY §4.2 -- the assigner is fed these pixel boxes (the CUDA path's own
+    decode) instead of this function's, so that a 1-ulp decode difference cannot flip a near-tie of two IoUs; the
+    loss terms still use this function's own decode."""
     B = feats[0].shape[0]
     no = nc + 4 * reg_max
     flat = torch.cat([f.view(B, no, -1) for f in feats], 2)                       # :391
@@ -236,8 +264,9 @@ def detection_loss(feats: Sequence[torch.Tensor], batch: Dict[str, torch.Tensor]
     gt_labels, gt_bboxes, mask_gt = t[..., 0], t[..., 1:5], (t[..., 5] > 0).float()     # :404-405
     anc, st = anchors_for([f.shape[2:] for f in feats], strides)                   # :408
     pred_bboxes = ltrb_to_xyxy(decode_ltrb(pred_distri, reg_max), anc.unsqueeze(0))  # :409
+    boxes_for_assign = (pred_bboxes * st).detach() if assign_boxes_px is None else assign_boxes_px
     labels, tboxes, tscores, fg, tgi = assign(pred_scores.detach().sigmoid(),
-                                              (pred_bboxes * st).detach(), anc * st,
+                                              boxes_for_assign, anc * st,
                                               gt_labels, gt_bboxes, mask_gt, nc, alpha, beta)  # :415-422
     # :424-470 emergency fallback is unreachable: loop 1 guarantees a positive per valid GT.
     tss = max(tscores.sum(), 1)                                                    # :472

@@ -70,6 +70,26 @@ def test_nms_class_aware_vs_oracle(cuda_lib):
         assert np.array_equal(ka[b, :int(kc[b])].cpu().numpy(), src[keep])
 
 
+@pytest.mark.parametrize("name", golden_names("nmsclass"))
+def test_nms_class_aware_golden(cuda_lib, name):
+    """Class-aware mode against keep lists produced by the reference's own nms_simple run once per class
+    subset (tests/golden/make_golden_r2.py), through the batched entry point and through nms_simple(labels=)."""
+    from oracle import c_oracle
+    from yolo_scratch_b200.train_yolo11_cuda import nms_batched, nms_simple
+    g = load_golden(name)
+    pred = t(g["pred"])
+    conf, thr = float(g["conf"]), float(g["iou"])
+    ka, _, _, kl, kc = nms_batched(pred.cuda(), conf, thr, 640, class_aware=True)
+    ka0, _, _, _, kc0 = nms_batched(pred.cuda(), conf, thr, 640)
+    for b in range(pred.shape[0]):
+        assert np.array_equal(ka[b, :int(kc[b])].cpu().numpy(), g[f"keep{b}"])
+        assert np.array_equal(ka0[b, :int(kc0[b])].cpu().numpy(), g[f"keep_agnostic{b}"])
+        xyxy, sc, cl, src = c_oracle.filter_candidates(pred[b], conf)
+        keep = nms_simple(torch.from_numpy(xyxy).cuda(), torch.from_numpy(sc).cuda(), thr, labels=torch.from_numpy(cl).cuda())
+        assert np.array_equal(src[keep], g[f"keep{b}"])
+        assert np.array_equal(kl[b, :int(kc[b])].cpu().numpy(), cl[np.searchsorted(src, g[f"keep{b}"])])
+
+
 def test_nms_simple_and_iou_helpers(cuda_lib):
     from oracle import ref_port as orc, c_oracle
     from yolo_scratch_b200.train_yolo11_cuda import nms_simple, calculate_iou_batch_simple

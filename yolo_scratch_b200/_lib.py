@@ -47,6 +47,8 @@ PROTOTYPES = {
     "ys_match_detections": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_float,
                                     C.POINTER(C.c_double), c_int, c_void_p, c_void_p, c_void_p]),
     "ys_cda_nms": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, C.c_double, c_void_p, c_void_p, c_void_p]),
+    "ys_bbox_loss_workspace_bytes": (c_size_t, [c_int]),
+    "ys_bbox_loss": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p] * 3 + [c_void_p, c_size_t, c_void_p]),
     "ys_bbox_iou": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
 }
 
@@ -99,6 +101,28 @@ def ptr(t) -> int:
 def require_cuda(t: torch.Tensor, name: str):
     if not t.is_cuda:
         raise YsError(f"{name} must be a CUDA tensor: the B200 hot path has no CPU fallback")
+
+
+class on_device:
+    """`with on_device(t0, t1, ...):` -- every tensor must live on ONE CUDA device, which becomes the current device
+    for the ctypes launches inside (the library launches on the process's current device; a tensor on another GPU
+    would otherwise give illegal addresses or a stream of the wrong device)."""
+
+    def __init__(self, *tensors):
+        devs = {t.device for t in tensors if t is not None}
+        if len(devs) != 1:
+            raise YsError(f"all tensors of one call must be on the same CUDA device, got {sorted(map(str, devs))}")
+        (self.dev,) = devs
+        if self.dev.type != "cuda":
+            raise YsError("the B200 hot path has no CPU fallback: tensors must be CUDA tensors")
+        self.ctx = torch.cuda.device(self.dev)
+
+    def __enter__(self):
+        self.ctx.__enter__()
+        return self.dev
+
+    def __exit__(self, *exc):
+        return self.ctx.__exit__(*exc)
 
 
 class Workspace:

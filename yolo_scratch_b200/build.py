@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libys_b200.so")
-SOURCES = ["ys_api.cu", "ys_loss.cu", "ys_nms.cu", "ys_decode.cu", "ys_metrics.cu"]
+SOURCES = ["ys_api.cu", "ys_loss.cu", "ys_nms.cu", "ys_decode.cu", "ys_metrics.cu", "ys_bboxloss.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

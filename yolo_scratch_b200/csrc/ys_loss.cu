@@ -333,300 +333,6 @@ k_pack_gt_small(LevelSet L, const long long *__restrict__ batch_idx, const long 
     }
 }
 
-// =====================================================================================================
-// Loss forward + backward
-// =====================================================================================================
-// One launch, two warp roles, every warp an independent work item (no intra-block exchange until the final
-// partial sums).  Work items are numbered image-major so both roles of an image run close in time:
-//   box role    one warp = one 32-anchor segment of one level of one image, one lane per anchor, 64 box
-//               channels.  Each channel row of a segment is one 128-byte line.  Segments without a foreground
-//               anchor only zero-fill their gradient rows; foreground lanes run softmax statistics -> decode ->
-//               CIoU value + gradient -> DFL cross-entropy, then stream the 64 gradients out.
-//   class role  one warp = 128 anchors (float4 per lane) x 16 class channels.  BCE-with-logits forward and
-//               backward per element: one ex2, one rcp, a degree-7 polynomial for log1p -- no divisions.
-// The last block to finish reduces the per-block partial sums in a fixed order (fp64) and writes the loss.
-constexpr int kLossThreads = 256;
-constexpr int kLossWarps = kLossThreads / 32;
-constexpr int kClsGroup = 16;       // class channels per class-role work item
-constexpr int kClsBatch = 4;        // float4 loads in flight per lane
-
-struct LossParams {
-    const int *tgi;          // (B,A) -1 = background
-    const int *lab;          // (B,A) class of the assigned GT, -1 = background
-    const float *norm;       // (B,A)
-    const int *gt_off;       // (B+1)
-    const float4 *gt_box;    // px
-    const float4 *pbox;      // (B,A) decoded boxes, px (written by k_assign)
-    const float *tss;        // [0]
-    float4 *partials;        // (gridDim.x): box, cls, dfl partial sums (unnormalised)
-    unsigned *done;          // arrival counter, self-resetting
-    float *loss_out;         // [4]
-    int nc, n_groups;        // class channels, ceil(nc / kClsGroup)
-    int items_per_img;       // n_segs + n_chunks * n_groups
-    int total_items;         // B * items_per_img
-    float hyp_box, hyp_cls, hyp_dfl;
-    float batch;             // (float)B
-};
-
-// Register-resident 4-entry tables indexed by a loop counter that is deliberately NOT unrolled (keeps one side's
-// 16 logits live at a time instead of letting the compiler hoist all 64 loads).
-template <typename T> __device__ __forceinline__ T sel4(const T (&a)[4], int s) {
-    return s == 0 ? a[0] : (s == 1 ? a[1] : (s == 2 ? a[2] : a[3]));
-}
-template <typename T> __device__ __forceinline__ void put4(T (&a)[4], int s, T v) {
-    a[0] = s == 0 ? v : a[0]; a[1] = s == 1 ? v : a[1]; a[2] = s == 2 ? v : a[2]; a[3] = s == 3 ? v : a[3];
-}
-
-// Zero-fill the 64 box-gradient rows of one 32-anchor segment: 8 lanes per 128-byte row, 4 rows per instruction.
-__device__ __forceinline__ void zero_box_rows(float *g0, int hw, int i0, int lane) {
-    const int piece = (lane & 7) * 4, rsub = lane >> 3;
-    if (i0 + piece < hw) {     // hw % 4 == 0: the 4 anchors of a piece are live together
-        float *p = g0 + (size_t)rsub * hw + piece;
-        const size_t step = (size_t)4 * hw;
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int c = 0; c < 16; ++c) {
-            *reinterpret_cast<float4 *>(p) = z4;
-            p += step;
-        }
-    }
-}
-
-template <bool WRITE_GRAD>
-__device__ __forceinline__ void loss_box_segment(const LevelSet &L, const LossParams &P, int b, int seg, int lane,
-                                                 float inv_tss, float &acc_box, float &acc_dfl) {
-    int l = 0;
-#pragma unroll
-    for (int k = 1; k < YS_MAX_LEVELS; ++k)
-        if (k < L.n && seg >= L.seg_off[k]) l = k;
-    const int hw = L.hw[l], w = L.w[l];
-    const float st = L.stride[l];
-    const int i0 = (seg - L.seg_off[l]) * kSeg;
-    const int i = i0 + lane;
-    const bool live = i < hw;
-    const size_t img = (size_t)b * L.C * hw;
-    const size_t arow = (size_t)b * L.A + L.a_off[l] + i;
-    const int tg = live ? __ldg(P.tgi + arow) : -1;
-    const bool fg = tg >= 0;
-    if (!__any_sync(0xffffffffu, fg)) {
-        if (WRITE_GRAD) zero_box_rows(L.g[l] + img + i0, hw, i0, lane);
-        return;
-    }
-    // ---- per-anchor scalars.  Background lanes keep gd = cdfl = 0, which makes every gradient they emit +0.
-    float gd[4] = {0.f, 0.f, 0.f, 0.f};       // d(total)/d(d_s) from the CIoU term
-    float tt[4] = {0.f, 0.f, 0.f, 0.f};       // DFL targets (ltrb, grid units)
-    float cdfl = 0.f, wgt = 0.f;
-    if (fg) {
-        wgt = __ldg(P.norm + arow);                                                   // target_scores.sum(-1) (:298)
-        const float4 q = __ldg(P.gt_box + __ldg(P.gt_off + b) + tg);
-        const float4 tb = make_float4(q.x / st, q.y / st, q.z / st, q.w / st);        // target_bboxes /= stride (:479)
-        const float4 pp = __ldg(P.pbox + arow);                                       // decoded by k_assign, pixels
-        const float4 pb = make_float4(pp.x / st, pp.y / st, pp.z / st, pp.w / st);    // back to grid units (:412)
-        const int iy = i / w, ix = i - iy * w;
-        const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
-        tt[0] = gx - tb.x; tt[1] = gy - tb.y; tt[2] = tb.z - gx; tt[3] = tb.w - gy;   // bbox2dist (:304, :327-330)
-        float g4[4];
-        const float ciou = ciou_with_grad(pb, tb, g4);
-        acc_box += (1.0f - ciou) * wgt;
-        const float kb = -(P.hyp_box * P.batch * inv_tss) * wgt;                      // L = (1-ciou)*w/tss
-        // d/d(dist): x1 = gx - d0 -> -g4[0]; y1 -> -g4[1]; x2 = gx + d2 -> g4[2]; y2 -> g4[3]
-        gd[0] = kb * -g4[0]; gd[1] = kb * -g4[1]; gd[2] = kb * g4[2]; gd[3] = kb * g4[3];
-        cdfl = P.hyp_dfl * P.batch * inv_tss * 0.25f * wgt;
-    }
-    // ---- one pass over the four sides: softmax statistics, DFL cross-entropy and all 16 gradients of a side
-    //      from the same 16 exponentials.
-    const float *xs = L.x[l] + img + i;
-    float *gs = WRITE_GRAD ? (L.g[l] + img + i) : nullptr;
-    float ce = 0.f;
-#pragma unroll 1
-    for (int s = 0; s < 4; ++s) {
-        float z[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) z[j] = fg ? __ldg(xs + (size_t)j * hw) : 0.f;
-        float m = z[0];
-#pragma unroll
-        for (int j = 1; j < 16; ++j) m = fmaxf(m, z[j]);
-        const float mm = m * kLog2e;
-        float ssum = 0.f, dsum = 0.f;
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            z[j] = ex2_fast(fmaf(z[j], kLog2e, -mm));
-            ssum += z[j];
-            dsum = fmaf(z[j], (float)j, dsum);
-        }
-        const float inv = rcp_fast(ssum);
-        const float d = dsum * inv;
-        const float t = fminf(fmaxf(sel4(tt, s), 0.f), 14.99f);                       // reg_max - 1 - 0.01 (:304)
-        const int tli = (int)t;
-        const float wls = (float)(tli + 1) - t, wrs = 1.0f - wls;
-        float zl = 0.f, zr = 0.f;
-        if (fg) {
-            zl = __ldg(xs + (size_t)tli * hw);
-            zr = __ldg(xs + (size_t)(tli + 1) * hw);
-        }
-        // cross-entropy at bins tl and tl+1 (:315-324): logsumexp = (mm + log2(sum)) * ln2
-        const float lse = (mm + __log2f(ssum)) * 0.69314718055994531f;
-        ce += (lse - zl) * wls + (lse - zr) * wrs;
-        if (WRITE_GRAD) {
-            // g_j = p_j * (gd*(j - d) + cdfl) - cdfl * ([j == tl] * wl + [j == tl+1] * wr),  p_j = e_j * inv
-            const float gds = sel4(gd, s);
-            const float ka = inv * gds, kb0 = inv * fmaf(-gds, d, cdfl);
-            if (live) {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) gs[(size_t)j * hw] = z[j] * fmaf(ka, (float)j, kb0);
-            }
-            if (fg) {      // the two target bins get their one-hot part (same thread, same address: ordered)
-                const float el = ex2_fast(fmaf(zl, kLog2e, -mm)), er = ex2_fast(fmaf(zr, kLog2e, -mm));
-                gs[(size_t)tli * hw] = fmaf(el, fmaf(ka, (float)tli, kb0), -cdfl * wls);
-                gs[(size_t)(tli + 1) * hw] = fmaf(er, fmaf(ka, (float)(tli + 1), kb0), -cdfl * wrs);
-            }
-        }
-        xs += (size_t)16 * hw;
-        if (WRITE_GRAD) gs += (size_t)16 * hw;
-    }
-    acc_dfl += ce * 0.25f * wgt;                                                      // mean over 4 sides (:324) * weight
-}
-
-template <bool WRITE_GRAD>
-__device__ __forceinline__ void loss_cls_item(const LevelSet &L, const LossParams &P, int b, int chunk, int group,
-                                              int lane, float inv_tss, float &acc_cls) {
-    int l = 0;
-#pragma unroll
-    for (int k = 1; k < YS_MAX_LEVELS; ++k)
-        if (k < L.n && chunk >= L.chunk_off[k]) l = k;
-    const int hw = L.hw[l];
-    const int i0 = (chunk - L.chunk_off[l]) * kChunk + lane * 4;    // hw % 4 == 0 => the 4 anchors are live together
-    if (i0 >= hw) return;
-    const int c_lo = group * kClsGroup;
-    const int c_n = min(kClsGroup, P.nc - c_lo);
-    const size_t off = ((size_t)b * L.C + 64 + c_lo) * hw + i0;
-    const float *xc = L.x[l] + off;
-    float *gc = WRITE_GRAD ? L.g[l] + off : nullptr;
-    const size_t arow = (size_t)b * L.A + L.a_off[l] + i0;
-    const int4 lab4 = __ldg(reinterpret_cast<const int4 *>(P.lab + arow));
-    const float4 nr4 = __ldg(reinterpret_cast<const float4 *>(P.norm + arow));
-    // the class of anchor k relative to this item's first channel (never matches when background: lab = -1)
-    const int r0 = lab4.x - c_lo, r1 = lab4.y - c_lo, r2 = lab4.z - c_lo, r3 = lab4.w - c_lo;
-    const float gscale = P.hyp_cls * P.batch * inv_tss;
-    // targets pre-multiplied by the gradient scale: grad = sig*gscale - t*gscale, and sum(x*t) = sum(x*t*gscale)/gscale
-    // (hyp_cls == 0 makes the reported class loss 0 whatever this sum is)
-    const float inv_g = gscale != 0.f ? 1.0f / gscale : 0.f;
-    const float t0 = nr4.x * gscale, t1 = nr4.y * gscale, t2 = nr4.z * gscale, t3 = nr4.w * gscale;
-    // loss = sum max(x,0) - sum x*t + sum log1p(exp(-|x|)); the last sum is ONE log1p per lane of
-    // S = prod(1 + e) - 1, carried as S <- S + e + S*e (four independent chains, 16 factors each, S < 2^16).
-    float pos = 0.f, xt = 0.f;
-    float S0 = 0.f, S1 = 0.f, S2 = 0.f, S3 = 0.f;
-    auto elem = [&](float x, float tk, float &S) -> float {
-        const float e = ex2_fast(fabsf(x) * -kLog2e);      // exp(-|x|) in (0,1]
-        const float inv = rcp_fast(1.0f + e);               // sigmoid(|x|)
-        const float sg = x >= 0.f ? inv : e * inv;
-        S = fmaf(S, e, S + e);
-        pos += fmaxf(x, 0.f);
-        xt = fmaf(x, tk, xt);
-        return fmaf(sg, gscale, -tk);
-    };
-    auto one = [&](const float4 xv, int c) -> float4 {
-        float4 o;
-        o.x = elem(xv.x, c == r0 ? t0 : 0.f, S0);
-        o.y = elem(xv.y, c == r1 ? t1 : 0.f, S1);
-        o.z = elem(xv.z, c == r2 ? t2 : 0.f, S2);
-        o.w = elem(xv.w, c == r3 ? t3 : 0.f, S3);
-        return o;
-    };
-    if (c_n == kClsGroup) {
-        // software pipeline: the loads of batch h+1 are in flight while batch h is computed and stored
-        float4 cur[kClsBatch], nxt[kClsBatch];
-#pragma unroll
-        for (int u = 0; u < kClsBatch; ++u) cur[u] = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)u * hw));
-#pragma unroll
-        for (int h = 0; h < kClsGroup; h += kClsBatch) {
-            if (h + kClsBatch < kClsGroup) {
-#pragma unroll
-                for (int u = 0; u < kClsBatch; ++u)
-                    nxt[u] = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)(h + kClsBatch + u) * hw));
-            }
-#pragma unroll
-            for (int u = 0; u < kClsBatch; ++u) {
-                const float4 o = one(cur[u], h + u);
-                if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)(h + u) * hw) = o;
-            }
-#pragma unroll
-            for (int u = 0; u < kClsBatch; ++u) cur[u] = nxt[u];
-        }
-    } else {
-        for (int c = 0; c < c_n; ++c) {
-            const float4 xv = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)c * hw));
-            const float4 o = one(xv, c);
-            if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)c * hw) = o;
-        }
-    }
-    const float S01 = fmaf(S0, S1, S0 + S1), S23 = fmaf(S2, S3, S2 + S3);
-    acc_cls += pos - xt * inv_g + log1pf(fmaf(S01, S23, S01 + S23));
-}
-
-template <bool WRITE_GRAD>
-__global__ void __launch_bounds__(kLossThreads, 4) k_loss(LevelSet L, LossParams P) {
-    __shared__ float s_sum[kLossWarps][3];
-    __shared__ double s_fin[kLossWarps][3];
-    __shared__ int s_last;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int item = blockIdx.x * kLossWarps + warp;
-    const float inv_tss = 1.0f / P.tss[0];
-    float acc_box = 0.f, acc_cls = 0.f, acc_dfl = 0.f;
-    if (item < P.total_items) {
-        const int b = item / P.items_per_img;
-        const int r = item - b * P.items_per_img;
-        if (r < L.n_segs) {
-            loss_box_segment<WRITE_GRAD>(L, P, b, r, lane, inv_tss, acc_box, acc_dfl);
-        } else {
-            const int q = r - L.n_segs;
-            const int chunk = q / P.n_groups;
-            loss_cls_item<WRITE_GRAD>(L, P, b, chunk, q - chunk * P.n_groups, lane, inv_tss, acc_cls);
-        }
-    }
-    // ------------------------------------------------------------------ block partial sums (fixed order)
-    acc_box = warp_sum(acc_box);
-    acc_cls = warp_sum(acc_cls);
-    acc_dfl = warp_sum(acc_dfl);
-    if (lane == 0) { s_sum[warp][0] = acc_box; s_sum[warp][1] = acc_cls; s_sum[warp][2] = acc_dfl; }
-    __syncthreads();
-    if (tid == 0) {
-        float t0 = 0.f, t1 = 0.f, t2 = 0.f;
-#pragma unroll
-        for (int w = 0; w < kLossWarps; ++w) { t0 += s_sum[w][0]; t1 += s_sum[w][1]; t2 += s_sum[w][2]; }
-        P.partials[blockIdx.x] = make_float4(t0, t1, t2, 0.f);
-        __threadfence();
-        const unsigned prev = atomicAdd(P.done, 1u);
-        s_last = (prev == gridDim.x - 1u);
-    }
-    __syncthreads();
-    if (!s_last) return;
-    // ------------------------------------------------------------------ last block: ordered fp64 reduction
-    __threadfence();
-    double a0 = 0, a1 = 0, a2 = 0;
-    for (int i = tid; i < (int)gridDim.x; i += kLossThreads) {
-        const float4 v = __ldcg(P.partials + i);
-        a0 += v.x; a1 += v.y; a2 += v.z;
-    }
-    a0 = warp_sum(a0); a1 = warp_sum(a1); a2 = warp_sum(a2);
-    if (lane == 0) { s_fin[warp][0] = a0; s_fin[warp][1] = a1; s_fin[warp][2] = a2; }
-    __syncthreads();
-    if (tid == 0) {
-        double t0 = 0, t1 = 0, t2 = 0;
-        for (int w = 0; w < kLossWarps; ++w) { t0 += s_fin[w][0]; t1 += s_fin[w][1]; t2 += s_fin[w][2]; }
-        const double inv = 1.0 / (double)P.tss[0];
-        // loss[0] = box/tss*hyp_box, loss[1] = cls/tss*hyp_cls, loss[2] = dfl/tss*hyp_dfl (:475, :300, :306, :495-497)
-        const float lb = (float)(t0 * inv) * P.hyp_box;
-        const float lc = (float)(t1 * inv) * P.hyp_cls;
-        const float ld = (float)(t2 * inv) * P.hyp_dfl;
-        P.loss_out[0] = (lb + lc + ld) * P.batch;   // loss.sum() * batch_size (:499)
-        P.loss_out[1] = lb;
-        P.loss_out[2] = lc;
-        P.loss_out[3] = ld;
-        *P.done = 0u;
-    }
-}
-
 __global__ void k_scale_inplace(float *__restrict__ data, size_t n, const float *__restrict__ scale) {
     const float s = *scale;
     if (s == 1.0f) return;
@@ -800,11 +506,6 @@ struct LossWorkspace {
 };
 
 static inline int scan_blocks(int A) { return (A + kScanThreads - 1) / kScanThreads + YS_MAX_LEVELS; }   // upper bound (per-level cut)
-static inline size_t loss_items_bound(int B, int A, int nc) {
-    const size_t per_img = (size_t)A / kSeg + YS_MAX_LEVELS + ((size_t)A / kChunk + YS_MAX_LEVELS) * ((nc + kClsGroup - 1) / kClsGroup);
-    return (size_t)B * per_img;
-}
-
 static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, int n_gt, int nc) {
     Carver c(base, cap);
     const size_t N = (size_t)(n_gt > 0 ? n_gt : 1);
@@ -827,7 +528,7 @@ static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, i
     W.lab = c.take<int>((size_t)B * A);
     W.norm = c.take<float>((size_t)B * A);
     W.pbox = c.take<float4>((size_t)B * A);
-    W.partials = c.take<float4>(loss_items_bound(B, A, nc) / kLossWarps + 2 + 4096);
+    W.partials = c.take<float4>(4096 + 2);      // one per k_loss_stream CTA (the grid is capped at 4096)
     W.bytes = align_up(c.off, 256);
 }
 
@@ -935,7 +636,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         YS_CHECK_LAUNCH("k_assign");
     }
 
-    if ((stages & YS_STAGE_LOSS) && !(stages & YS_STAGE_DIAG_LEGACY_LOSS)) {
+    if (stages & YS_STAGE_LOSS) {
         // persistent TMA-fed stream: one CTA per SM
         StreamParams P;
         P.tgi = io.tgi; P.lab = W.lab; P.norm = io.norm; P.gt_off = W.gt_off; P.gt_box = W.gt_box; P.pbox = io.pbox;
@@ -997,21 +698,6 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         }
         YS_REQUIRE(le == cudaSuccess, (int)le, "k_loss_stream launch: %s", cudaGetErrorString(le));
         YS_CHECK_LAUNCH("k_loss_stream");
-    } else if (stages & YS_STAGE_LOSS) {
-        LossParams P;
-        P.tgi = io.tgi; P.lab = W.lab; P.norm = io.norm; P.gt_off = W.gt_off; P.gt_box = W.gt_box; P.pbox = io.pbox;
-        P.tss = W.tss; P.partials = W.partials; P.done = W.counters + 1; P.loss_out = loss_out;
-        P.nc = nc; P.n_groups = (nc + kClsGroup - 1) / kClsGroup;
-        P.items_per_img = L.n_segs + L.n_chunks * P.n_groups;
-        P.total_items = B * P.items_per_img;
-        P.hyp_box = hyp_box; P.hyp_cls = hyp_cls; P.hyp_dfl = hyp_dfl; P.batch = (float)B;
-        YS_REQUIRE((long long)B * P.items_per_img < 2147483647LL, YS_ERR_UNSUPPORTED, "too many work items");
-        const unsigned blocks = (unsigned)((P.total_items + kLossWarps - 1) / kLossWarps);
-        if (level_grad_host)
-            k_loss<true><<<blocks, kLossThreads, 0, stream>>>(L, P);
-        else
-            k_loss<false><<<blocks, kLossThreads, 0, stream>>>(L, P);
-        YS_CHECK_LAUNCH("k_loss");
     }
     return YS_OK;
 }

@@ -339,15 +339,6 @@ k_nms_suppress(const int *__restrict__ count, int A, const float4 *__restrict__ 
     }
 }
 
-// ---------------------------------------------------------------------------------------------------
-// k_nms_suppress_reg: the same greedy suppression with the COLUMNS resident in registers.
-// One block of 1024 threads per image; thread t owns the sorted boxes t, t+1024, ... (COLS of them): box, area, class
-// and an alive bit per column live in registers, so the N^2/2 pair tests read only the 64 kept-row boxes of the
-// current tile (shared-memory broadcasts) -- no shared-memory box table, no index indirection, no atomics.
-// Per 64-row tile: owners publish the tile -> diagonal 64x64 bitmask by warp ballots -> one thread resolves the tile
-// serially (greedy order) and compacts the kept rows -> every thread tests its later, alive columns against them.
-// Keep lists are identical to k_nms_suppress (the arithmetic of a pair test is the same function).
-// ---------------------------------------------------------------------------------------------------
 constexpr int kRegThreads = 1024;
 
 // Half of the overlap a pair needs along one axis before IoU > thr is possible, charged to one box of extent [lo, hi]:
@@ -359,232 +350,6 @@ constexpr int kRegThreads = 1024;
 __device__ __forceinline__ float nms_shrink_half(float lo, float hi, float thr01) {
     const float h = __fsub_rn(__fmul_rn(0.495f * thr01, __fsub_rn(hi, lo)), 1.0e-6f * fmaxf(fabsf(lo), fabsf(hi)));
     return h > 0.f ? h : 0.f;
-}
-
-template <bool CLASS_AWARE, int COLS>
-__global__ void __launch_bounds__(kRegThreads, 1)
-k_nms_suppress_reg(const int *__restrict__ count, int A, const float4 *__restrict__ sbox, const float *__restrict__ sscore,
-                   const int *__restrict__ scls, const int *__restrict__ sanchor, float thr, float img_size,
-                   int *__restrict__ keep_anchor, float4 *__restrict__ keep_boxes, float *__restrict__ keep_scores,
-                   int *__restrict__ keep_labels, int *__restrict__ keep_count) {
-    __shared__ float4 s_tile[64];
-    __shared__ float s_tarea[64];
-    __shared__ int s_tcls[64];
-    __shared__ unsigned long long s_diag[64];
-    __shared__ float4 s_kbox[64];
-    __shared__ float4 s_kshr[64];      // the kept rows shrunk by nms_shrink_half (candidate test only)
-    __shared__ float s_karea[64];
-    __shared__ int s_kcls[64];
-    __shared__ unsigned s_talive[2];
-    __shared__ unsigned long long s_trem;
-    __shared__ int s_nk;
-    __shared__ unsigned s_alive[COLS * kRegThreads / 32];
-    const int b = blockIdx.x;
-    const int n = count[b];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (n == 0) {
-        if (tid == 0) keep_count[b] = 0;
-        return;
-    }
-    const float4 *gbox = sbox + (size_t)b * A;
-    const int *gcls = scls + (size_t)b * A;
-    float4 bx[COLS];
-    int cl[COLS];
-    unsigned alive = 0u;
-    bool sane = true;      // finite, well-formed boxes: a pair that does not intersect then has IoU exactly 0
-#pragma unroll
-    for (int k = 0; k < COLS; ++k) {
-        const int c = k * kRegThreads + tid;
-        bx[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        cl[k] = -1;
-        if (c < n) {
-            bx[k] = gbox[c];
-            if (CLASS_AWARE) cl[k] = gcls[c];
-            alive |= 1u << k;
-        }
-        sane = sane && (area_plain(bx[k]) >= 0.f) && (fabsf(bx[k].x) + fabsf(bx[k].y) + fabsf(bx[k].z) + fabsf(bx[k].w) < 3.0e38f);
-    }
-    for (int i = tid; i < COLS * kRegThreads / 32; i += kRegThreads) s_alive[i] = 0u;
-    sane = __syncthreads_and(sane) && (0.f <= thr);
-    const float thr01 = (thr >= 0.f && thr <= 1.f) ? thr : 0.f;      // outside [0,1] the candidate test is plain intersection
-
-    for (int t0 = 0; t0 < n; t0 += 64) {
-        const int tn = min(64, n - t0);
-        const int kt = t0 / kRegThreads, i_t = tid - (t0 - kt * kRegThreads);     // owners of the tile: 64 consecutive threads
-        if (i_t >= 0 && i_t < 64) {
-            float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
-            float ma = 0.f;
-            int mc = -1;
-            bool al = false;
-#pragma unroll
-            for (int k = 0; k < COLS; ++k)
-                if (k == kt) { mine = bx[k]; mc = cl[k]; al = (alive >> k) & 1u; }
-            ma = area_plain(mine);      // areas are recomputed where needed (same function, same bits): nine registers less
-            s_tile[i_t] = mine;
-            s_tarea[i_t] = ma;
-            if (CLASS_AWARE) s_tcls[i_t] = mc;
-            const unsigned m = __ballot_sync(0xffffffffu, al);      // the 64 owners are two whole warps (64 | 1024)
-            if (lane == 0) s_talive[i_t >> 5] = m;
-        }
-        __syncthreads();
-        // -- diagonal 64x64 bitmask tile by warp ballots: warp w handles rows w and w + 32
-        for (int r = warp; r < tn; r += kRegThreads / 32) {
-            const float4 bi = s_tile[r];
-            const float ai = s_tarea[r];
-            unsigned long long bits = 0ull;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int c = h * 32 + lane;
-                bool sup = false;
-                if (c > r && c < tn) {
-                    sup = suppresses(bi, ai, s_tile[c], thr);
-                    if (CLASS_AWARE) sup = sup && (s_tcls[c] == s_tcls[r]);
-                }
-                const unsigned m = __ballot_sync(0xffffffffu, sup);
-                bits |= (unsigned long long)m << (32 * h);
-            }
-            if (lane == 0) s_diag[r] = bits;
-        }
-        __syncthreads();
-        // -- greedy resolution of the tile by ONE WARP: the 64 row masks live in registers (two per lane), the running
-        //    "removed" mask is replicated in every lane, one shuffle per row; then the lanes compact the kept rows for
-        //    the column pass (rows of zero extent and the padding to a multiple of 8 -> (+inf,+inf,-inf,-inf): never a candidate)
-        if (warp == 0) {
-            const unsigned long long d0 = lane < tn ? s_diag[lane] : 0ull;
-            const unsigned long long d1 = lane + 32 < tn ? s_diag[lane + 32] : 0ull;
-            unsigned long long rem = ~((unsigned long long)s_talive[0] | ((unsigned long long)s_talive[1] << 32));
-            unsigned long long kept = 0ull;
-#pragma unroll
-            for (int r = 0; r < 64; ++r) {
-                const unsigned long long dr = __shfl_sync(0xffffffffu, r < 32 ? d0 : d1, r & 31);
-                if (!((rem >> r) & 1ull)) {      // uniform across the warp
-                    kept |= 1ull << r;
-                    rem |= dr;
-                }
-            }
-            const int nk = __popcll(kept);
-            const float pinf = __int_as_float(0x7f800000), ninf = __int_as_float(0xff800000);
-            const float4 never = make_float4(pinf, pinf, ninf, ninf);      // x2 - anything = -inf: never a candidate
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int r = lane + 32 * h;
-                if ((kept >> r) & 1ull) {
-                    const int pos = __popcll(kept & ((1ull << r) - 1ull));
-                    float4 v = s_tile[r];
-                    float4 sh = v;
-                    if (sane && !(v.z > v.x && v.w > v.y)) { v = never; sh = never; }
-                    else {
-                        const float hx = nms_shrink_half(v.x, v.z, thr01), hy = nms_shrink_half(v.y, v.w, thr01);
-                        sh = make_float4(__fadd_rn(v.x, hx), __fadd_rn(v.y, hy), __fsub_rn(v.z, hx), __fsub_rn(v.w, hy));
-                    }
-                    s_kbox[pos] = v;
-                    s_kshr[pos] = sh;
-                    s_karea[pos] = s_tarea[r];
-                    if (CLASS_AWARE) s_kcls[pos] = s_tcls[r];
-                }
-            }
-            if (lane < ((nk + 7) & ~7) - nk) { s_kbox[nk + lane] = never; s_kshr[nk + lane] = never; }
-            if (lane == 0) { s_nk = nk; s_trem = rem; }
-        }
-        __syncthreads();
-        const int nk = s_nk;
-        if (i_t >= 0 && i_t < 64 && ((s_trem >> i_t) & 1ull)) alive &= ~(1u << kt);      // removed inside the tile
-        // -- kept rows of this tile suppress every later, still-alive column (registers vs shared-memory broadcasts)
-        if (nk > 0) {
-#pragma unroll
-            for (int k = 0; k < COLS; ++k) {
-                const int c = k * kRegThreads + tid;
-                if (!((alive >> k) & 1u) || c < t0 + 64) continue;
-                const float4 bj = bx[k];
-                const float aj = area_plain(bj);
-                bool dead = false;
-                if (sane) {
-                    // Branch-free candidate pass: two boxes of positive extent intersect iff
-                    //   bi.z > bj.x && bj.z > bi.x && bi.w > bj.y && bj.w > bi.y
-                    // (min(a,b) - max(c,d) > 0 in fp32 <=> min(a,b) > max(c,d); the two remaining comparisons, each
-                    // box's own extent, are folded into the data: kept rows of zero extent were stored as (+inf,+inf,-inf,-inf), and
-                    // a column of zero extent has ok_j false).  The exact IoU runs only on the candidates.
-                    if (bj.z > bj.x && bj.w > bj.y) {
-                        // a > b  <=>  fl(a - b) > 0 for finite fp32 (gradual underflow; under flush-to-zero the sign
-                        // survives), so the four comparisons become four FADDs (fma pipe) and the pair's verdict is
-                        // the OR of the four sign bits (two LOP3) shifted into a mask (one SHF): 3 alu-pipe
-                        // instructions per pair instead of 4 FSETP + SEL + LOP3 -- the alu pipe was the limiter
-                        // (ncu: math-pipe throttle the top stall, 62 % issue).  A difference of +0 (touching boxes)
-                        // reads as a hit: a harmless false candidate, the exact IoU below says 0.
-                        // Both boxes are shrunk first (nms_shrink_half): a pair whose shrunken boxes do not intersect
-                        // cannot reach IoU > thr, so far fewer pairs go on to the exact IoU (random boxes at thr 0.7:
-                        // ~8x fewer candidates than plain intersection).
-                        float thr_k = thr01;
-                        asm volatile("" : "+f"(thr_k));      // keeps the (tile-invariant) shrunken column out of registers across tiles: recomputed here, ~12 instructions per 64 rows
-                        const float hx = nms_shrink_half(bj.x, bj.z, thr_k), hy = nms_shrink_half(bj.y, bj.w, thr_k);
-                        const float jx = __fadd_rn(bj.x, hx), jy = __fadd_rn(bj.y, hy), jz = __fsub_rn(bj.z, hx), jw = __fsub_rn(bj.w, hy);
-                        unsigned long long cand = 0ull;
-                        for (int q0 = 0; q0 < nk; q0 += 32) {         // s_kshr is padded with never-hit rows to a multiple of 8
-                            const int qe = min(32, ((nk + 7) & ~7) - q0);
-                            unsigned nm = 0u;                          // "no hit" bits, latest pair in bit 0
-                            for (int u0 = 0; u0 < qe; u0 += 8) {
-#pragma unroll
-                                for (int u = 0; u < 8; ++u) {
-                                    const float4 bi = s_kshr[q0 + u0 + u];
-                                    const int sg = __float_as_int(__fsub_rn(bi.z, jx)) | __float_as_int(__fsub_rn(jz, bi.x)) |
-                                                   __float_as_int(__fsub_rn(bi.w, jy)) | __float_as_int(__fsub_rn(jw, bi.y));
-                                    nm = __funnelshift_l((unsigned)sg, nm, 1);
-                                }
-                            }
-                            const unsigned hits = (~__brev(nm)) >> (32 - qe);      // pair q0 + i -> bit i
-                            cand |= (unsigned long long)hits << q0;
-                        }
-                        while (cand && !dead) {
-                            const int q = __ffsll((long long)cand) - 1;
-                            cand &= cand - 1ull;
-                            if (CLASS_AWARE && s_kcls[q] != cl[k]) continue;
-                            const float iou = iou_nms(s_kbox[q], s_karea[q], bj, aj);
-                            dead = !(iou <= thr);
-                        }
-                    }
-                } else {
-                    for (int q = 0; q < nk && !dead; ++q) {
-                        if (CLASS_AWARE && s_kcls[q] != cl[k]) continue;
-                        dead = suppresses(s_kbox[q], s_karea[q], bj, thr);
-                    }
-                }
-                if (dead) alive &= ~(1u << k);
-            }
-        }
-        // no barrier here: the next tile's first barrier orders these reads of s_k* before thread 0 rewrites them
-    }
-
-    // -- survivors: bitmap in sorted order, then one warp compacts (ballot prefix)
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < COLS; ++k)
-        if ((alive >> k) & 1u) atomicOr(&s_alive[(k * kRegThreads + tid) >> 5], 1u << (tid & 31));
-    __syncthreads();
-    if (warp == 0) {
-        int base = 0;
-        for (int c0 = 0; c0 < n; c0 += 32) {
-            const int c = c0 + lane;
-            const bool al = c < n && ((s_alive[c >> 5] >> (c & 31)) & 1u);
-            const unsigned m = __ballot_sync(0xffffffffu, al);
-            if (al) {
-                const size_t o = (size_t)b * A + base + __popc(m & ((1u << lane) - 1u));
-                const size_t s = (size_t)b * A + c;
-                if (keep_anchor) keep_anchor[o] = sanchor[s];
-                if (keep_boxes) {
-                    const float4 v = sbox[s];
-                    // boxes / img_size, clamp to [0,1]  (train_yolo11_cuda.py:347-350)
-                    float4 q = make_float4(YS_DIV(v.x, img_size), YS_DIV(v.y, img_size), YS_DIV(v.z, img_size), YS_DIV(v.w, img_size));
-                    q.x = fminf2(fmaxf2(q.x, 0.f), 1.f); q.y = fminf2(fmaxf2(q.y, 0.f), 1.f);
-                    q.z = fminf2(fmaxf2(q.z, 0.f), 1.f); q.w = fminf2(fmaxf2(q.w, 0.f), 1.f);
-                    keep_boxes[o] = q;
-                }
-                if (keep_scores) keep_scores[o] = sscore[s];
-                if (keep_labels) keep_labels[o] = scls[s];
-            }
-            base += __popc(m);
-        }
-        if (lane == 0) keep_count[b] = base;
-    }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -791,7 +556,7 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
             if (lane == 0) s_diag[r] = bits;
         }
         __syncthreads();
-        // -- greedy resolution of the tile by one warp (as in k_nms_suppress_reg); the rows' alive bits come from, and
+        // -- greedy resolution of the tile by one warp ; the rows' alive bits come from, and
         //    go back to, the rank-indexed bitmap (nobody else touches the tile's two words now: column passes only
         //    clear bits of ranks >= t0 + 64)
         if (warp == 0) {
@@ -882,7 +647,7 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
                             const int q = __ffs((int)m) - 1 + 32 * h;
                             m &= m - 1u;
                             const float4 bi = s_kshr[q];
-                            // a > b  <=>  fl(a - b) > 0: four FADD sign bits (see k_nms_suppress_reg); +0 reads as a hit
+                            // a > b  <=>  fl(a - b) > 0: four FADD sign bits ; +0 reads as a hit
                             const int sg = __float_as_int(__fsub_rn(bi.z, jx)) | __float_as_int(__fsub_rn(jz, bi.x)) |
                                            __float_as_int(__fsub_rn(bi.w, jy)) | __float_as_int(__fsub_rn(jw, bi.y));
                             if (sg >= 0) {
@@ -1002,23 +767,15 @@ static int run_sort_suppress(const NmsWorkspace &W, int B, int A, float iou_thr,
     k_nms_sort<<<B, kSortThreads, sort_smem, stream>>>(W.keys, W.count, A, boxes, cls, W.sbox, W.sscore, W.scls, W.sanchor);
     YS_CHECK_LAUNCH("k_nms_sort");
     if (A <= 9 * kRegThreads) {      // register-resident columns (every 640 px / 8400-candidate case)
-#ifndef YS_NMS_ZORDER
-#define YS_NMS_ZORDER 1      // 0: k_nms_suppress_reg (columns in rank order), kept for A/B
-#endif
-#if YS_NMS_ZORDER
-#define YS_NMS_REG_KERNEL k_nms_suppress_zreg
-#else
-#define YS_NMS_REG_KERNEL k_nms_suppress_reg
-#endif
 #define YS_LAUNCH_REG(CA, COLS)                                                                                              \
-    YS_NMS_REG_KERNEL<CA, COLS><<<B, kRegThreads, 0, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr,      \
+    k_nms_suppress_zreg<CA, COLS><<<B, kRegThreads, 0, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr,      \
                                                                 img_size, keep_anchor, (float4 *)keep_boxes, keep_scores,     \
                                                                 keep_labels, keep_count)
         if (A <= 2 * kRegThreads) { if (class_aware) YS_LAUNCH_REG(true, 2); else YS_LAUNCH_REG(false, 2); }
         else if (A <= 5 * kRegThreads) { if (class_aware) YS_LAUNCH_REG(true, 5); else YS_LAUNCH_REG(false, 5); }
         else { if (class_aware) YS_LAUNCH_REG(true, 9); else YS_LAUNCH_REG(false, 9); }
 #undef YS_LAUNCH_REG
-        YS_CHECK_LAUNCH("k_nms_suppress_reg");
+        YS_CHECK_LAUNCH("k_nms_suppress_zreg");
         return YS_OK;
     }
     const int smem_boxes = A <= kSupSmemBoxes ? A : 0;

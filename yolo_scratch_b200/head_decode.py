@@ -29,8 +29,9 @@ def detect_inference(feats, nc, reg_max=16, strides=(8, 16, 32), anchor_major=Fa
     hs = (C.c_int * n)(*[x.shape[2] for x in xs])
     ws = (C.c_int * n)(*[x.shape[3] for x in xs])
     st = (C.c_float * n)(*[float(s) for s in list(strides)[:n]])
-    check(_lib.lib().ys_decode_infer(n, xp, hs, ws, st, B, nc, reg_max, ptr(out), 1 if anchor_major else 0,
-                                     stream_ptr(dev)), "ys_decode_infer")
+    with _lib.on_device(*xs):
+        check(_lib.lib().ys_decode_infer(n, xp, hs, ws, st, B, nc, reg_max, ptr(out), 1 if anchor_major else 0,
+                                         stream_ptr(dev)), "ys_decode_infer")
     return out
 
 

@@ -59,15 +59,14 @@ class _BboxIoU(torch.autograd.Function):
     """Paired-box IoU family through ys_bbox_iou; gradient wrt box1 for the CIoU/xyxy form BboxLoss uses."""
 
     @staticmethod
-    def forward(ctx, box1, box2, xywh, mode, eps):
+    def forward(ctx, box1, box2, xywh, mode, eps, want_grad):
         lib = _lib.lib()
         n = box1.shape[0]
         out = torch.empty(n, device=box1.device, dtype=torch.float32)
-        want_grad = box1.requires_grad
-        ctx.can_grad = (not xywh) and mode == 3 and abs(eps - 1e-7) < 1e-12
-        grad = torch.empty_like(box1) if (want_grad and ctx.can_grad) else None
-        check(lib.ys_bbox_iou(ptr(box1), ptr(box2), n, int(bool(xywh)), mode, float(eps), ptr(out), 0, ptr(grad),
-                              stream_ptr(box1.device)), "ys_bbox_iou")
+        grad = torch.empty_like(box1) if want_grad else None
+        with _lib.on_device(box1, box2):
+            check(lib.ys_bbox_iou(ptr(box1), ptr(box2), n, int(bool(xywh)), mode, float(eps), ptr(out), 0, ptr(grad),
+                                  stream_ptr(box1.device)), "ys_bbox_iou")
         ctx.save_for_backward(grad) if grad is not None else None
         ctx.has_grad = grad is not None
         return out
@@ -75,11 +74,9 @@ class _BboxIoU(torch.autograd.Function):
     @staticmethod
     def backward(ctx, gout):
         if not ctx.has_grad:
-            if not ctx.can_grad:
-                raise YsError("bbox_iou backward is implemented for xywh=False, CIoU=True, eps=1e-7 (the BboxLoss use)")
-            return None, None, None, None, None
+            return None, None, None, None, None, None
         (grad,) = ctx.saved_tensors
-        return grad * gout.unsqueeze(-1), None, None, None, None
+        return grad * gout.unsqueeze(-1), None, None, None, None, None
 
 
 def bbox_iou(box1, box2, xywh=True, GIoU=False, DIoU=False, CIoU=False, eps=1e-7):
@@ -87,11 +84,20 @@ def bbox_iou(box1, box2, xywh=True, GIoU=False, DIoU=False, CIoU=False, eps=1e-7
     (reference losses/yolo_v8_loss.py:12-61)."""
     _lib.require_cuda(box1, "box1")
     _lib.require_cuda(box2, "box2")
+    if torch.is_grad_enabled():
+        # The device kernel differentiates the BboxLoss form only: wrt box1, xyxy, CIoU, eps 1e-7 (reference :298).
+        # Anything else would silently drop gradients the reference's autograd provides, so it raises here.
+        if box2.requires_grad:
+            raise YsError("bbox_iou: gradient wrt box2 is not implemented (pass box2.detach(); targets carry no grad "
+                          "in the reference's loss, losses/yolo_v8_loss.py:416-417)")
+        if box1.requires_grad and not ((not xywh) and CIoU and abs(eps - 1e-7) < 1e-12):
+            raise YsError("bbox_iou: gradient wrt box1 is implemented for xywh=False, CIoU=True, eps=1e-7 only "
+                          "(the BboxLoss use); detach box1 or use that form")
     shape = torch.broadcast_shapes(box1.shape[:-1], box2.shape[:-1])
     b1 = box1.expand(*shape, 4).reshape(-1, 4).contiguous().float()
     b2 = box2.expand(*shape, 4).reshape(-1, 4).contiguous().float()
     mode = 3 if CIoU else 2 if DIoU else 1 if GIoU else 0
-    out = _BboxIoU.apply(b1, b2, bool(xywh), mode, float(eps))
+    out = _BboxIoU.apply(b1, b2, bool(xywh), mode, float(eps), torch.is_grad_enabled() and box1.requires_grad)
     return out.view(*shape, 1)
 
 
@@ -132,18 +138,53 @@ class TaskAlignedAssigner(nn.Module):
         fg = torch.empty(B, A, device=dev, dtype=torch.uint8)
         tgi = torch.empty(B, A, device=dev, dtype=torch.int64)
         ws = self._ws.get(lib.ys_assign_workspace_bytes(B, A, G), dev)
-        check(lib.ys_assign(B, A, G, self.num_classes, ptr(ps), ptr(pb), ptr(an), ptr(gl), ptr(gb), ptr(mg),
-                            float(self.alpha), float(self.beta), float(self.eps), ptr(tl), ptr(tb), ptr(ts), ptr(fg),
-                            ptr(tgi), 0, ptr(ws), ws.numel(), stream_ptr(dev)), "ys_assign")
+        with _lib.on_device(ps):
+            check(lib.ys_assign(B, A, G, self.num_classes, ptr(ps), ptr(pb), ptr(an), ptr(gl), ptr(gb), ptr(mg),
+                                float(self.alpha), float(self.beta), float(self.eps), ptr(tl), ptr(tb), ptr(ts), ptr(fg),
+                                ptr(tgi), 0, ptr(ws), ws.numel(), stream_ptr(dev)), "ys_assign")
         return tl, tb, ts, fg.bool(), tgi
 
 
 # ----------------------------------------------------------------------------------------------
 # BboxLoss (stand-alone use; the fused loss below does not go through it)
 # ----------------------------------------------------------------------------------------------
+class _BboxLossFn(torch.autograd.Function):
+    """ys_bbox_loss: both loss terms and their gradients wrt pred_dist / pred_bboxes in one launch."""
+
+    @staticmethod
+    def forward(ctx, pred_dist, pred_bboxes, anchor_points, target_bboxes, target_scores, tss, fg_mask, reg_max, want_grad):
+        lib = _lib.lib()
+        dev = pred_dist.device
+        A = anchor_points.shape[0]
+        nc = target_scores.shape[-1]
+        n = fg_mask.numel()
+        f = lambda t: t.detach().to(device=dev, dtype=torch.float32).contiguous()
+        pd, pb, ap, tb, ts = f(pred_dist), f(pred_bboxes), f(anchor_points), f(target_bboxes), f(target_scores)
+        fg = fg_mask.detach().to(device=dev, dtype=torch.uint8).contiguous()
+        tss_d = f(tss).reshape(1)
+        out = torch.empty(2, device=dev)
+        g_pd = torch.empty_like(pd) if (want_grad and pred_dist.requires_grad) else None
+        g_pb = torch.empty_like(pb) if (want_grad and pred_bboxes.requires_grad) else None
+        ws = torch.empty(lib.ys_bbox_loss_workspace_bytes(n), dtype=torch.uint8, device=dev)
+        with _lib.on_device(pd):
+            check(lib.ys_bbox_loss(ptr(pd), ptr(pb), ptr(ap), ptr(tb), ptr(ts), ptr(fg), ptr(tss_d), n, A, nc, int(reg_max),
+                                   ptr(out), ptr(g_pb), ptr(g_pd), ptr(ws), ws.numel(), stream_ptr(dev)), "ys_bbox_loss")
+        ctx.g_pb = g_pb.view_as(pred_bboxes) if g_pb is not None else None
+        ctx.g_pd = g_pd.view_as(pred_dist) if g_pd is not None else None
+        return out[0], out[1]
+
+    @staticmethod
+    def backward(ctx, g_iou, g_dfl):
+        g_pb = ctx.g_pb * g_iou if ctx.g_pb is not None else None
+        g_pd = ctx.g_pd * g_dfl if ctx.g_pd is not None else None
+        return g_pd, g_pb, None, None, None, None, None, None, None
+
+
 class BboxLoss(nn.Module):
-    """CIoU + DFL on already-gathered tensors (reference losses/yolo_v8_loss.py:273-324).  The CIoU value
-    and its gradient come from ys_bbox_iou; the DFL term uses the two-sided cross-entropy of :312-324."""
+    """CIoU + DFL on already-assigned dense tensors: same constructor and forward contract as the reference class
+    (losses/yolo_v8_loss.py:273-324), computed by one kernel (ys_bbox_loss) instead of boolean-mask gathers.
+    Gradients flow to pred_dist and pred_bboxes; the targets carry none (they come out of a no_grad assigner,
+    reference :78, :416-417)."""
 
     def __init__(self, reg_max=16):
         super().__init__()
@@ -151,26 +192,11 @@ class BboxLoss(nn.Module):
 
     def forward(self, pred_dist, pred_bboxes, anchor_points, target_bboxes, target_scores, target_scores_sum, fg_mask):
         _lib.require_cuda(pred_dist, "pred_dist")
-        weight = target_scores.sum(-1)[fg_mask].unsqueeze(-1)
-        iou = bbox_iou(pred_bboxes[fg_mask], target_bboxes[fg_mask], xywh=False, CIoU=True)
-        loss_iou = ((1.0 - iou) * weight).sum() / target_scores_sum
-        if self.reg_max > 1:
-            target_ltrb = bbox2dist(anchor_points, target_bboxes, self.reg_max - 1)
-            loss_dfl = self._df_loss(pred_dist[fg_mask].view(-1, self.reg_max), target_ltrb[fg_mask]) * weight
-            loss_dfl = loss_dfl.sum() / target_scores_sum
-        else:
-            loss_dfl = torch.tensor(0.0).to(pred_dist.device)
-        return loss_iou, loss_dfl
-
-    @staticmethod
-    def _df_loss(pred_dist, target):
-        target = target.clamp_(0, pred_dist.shape[-1] - 1 - 0.01)
-        lo = target.long()
-        w_lo = (lo + 1) - target
-        logp = pred_dist.log_softmax(-1).view(*lo.shape, -1)
-        ce_lo = -logp.gather(-1, lo.unsqueeze(-1)).squeeze(-1)
-        ce_hi = -logp.gather(-1, (lo + 1).unsqueeze(-1)).squeeze(-1)
-        return (ce_lo * w_lo + ce_hi * (1 - w_lo)).mean(-1, keepdim=True)
+        if torch.is_grad_enabled() and (target_bboxes.requires_grad or target_scores.requires_grad):
+            raise YsError("BboxLoss: targets must not require grad (the assigner's outputs are detached in the reference)")
+        tss = target_scores_sum if torch.is_tensor(target_scores_sum) else torch.tensor(float(target_scores_sum))
+        return _BboxLossFn.apply(pred_dist, pred_bboxes, anchor_points, target_bboxes, target_scores, tss, fg_mask,
+                                 self.reg_max, torch.is_grad_enabled())
 
 
 # ----------------------------------------------------------------------------------------------
@@ -205,27 +231,37 @@ class _FusedDetectionLoss(torch.autograd.Function):
         # imgsz = feats[0].shape[2:] * stride[0]; x is scaled by imgsz[0], y by imgsz[1] (reference :400, :515)
         sx = float(xs[0].shape[2]) * float(owner.stride[0])
         sy = float(xs[0].shape[3]) * float(owner.stride[0])
-        check(lib.ys_detection_loss(n, xp, gp, hs, ws_, st, B, owner.nc, owner.reg_max, ptr(batch_idx), ptr(cls),
-                                    ptr(bboxes), n_gt, sx, sy, owner.hyp_box, owner.hyp_cls, owner.hyp_dfl,
-                                    float(owner.assigner.alpha), float(owner.assigner.beta), ptr(out), ptr(pb),
-                                    ptr(tgi), ptr(nrm), 0, ptr(ws), ws.numel(), stream_ptr(dev)), "ys_detection_loss")
+        with _lib.on_device(*xs, batch_idx, cls, bboxes):
+            check(lib.ys_detection_loss(n, xp, gp, hs, ws_, st, B, owner.nc, owner.reg_max, ptr(batch_idx), ptr(cls),
+                                        ptr(bboxes), n_gt, sx, sy, owner.hyp_box, owner.hyp_cls, owner.hyp_dfl,
+                                        float(owner.assigner.alpha), float(owner.assigner.beta), ptr(out), ptr(pb),
+                                        ptr(tgi), ptr(nrm), 0, ptr(ws), ws.numel(), stream_ptr(dev)), "ys_detection_loss")
         if export:
             owner.last_export = {"pred_bboxes_px": pb, "target_gt_idx": tgi, "norm": nrm}
         ctx.grads = grads
+        ctx.n_feats = n
+        ctx.consumed = False
         total, items = out[0], out[1:4]
         ctx.mark_non_differentiable(items)
         return total, items
 
     @staticmethod
     def backward(ctx, g_total, g_items):
+        if ctx.consumed:
+            # the gradients were computed by the forward call and handed over (scaled in place) by the first backward;
+            # like torch without retain_graph, a second pass needs a fresh forward
+            raise YsError("v8DetectionLoss: backward through the same loss twice is not supported (the fused kernel's "
+                          "gradient buffers are handed to autograd by the first backward); call the criterion again")
         grads = ctx.grads
-        if grads is None:
-            return (None,) * 5
+        if grads is None:        # no head tensor required grad
+            return (None,) * (5 + ctx.n_feats)
         lib = _lib.lib()
         g = g_total.detach().to(torch.float32).contiguous()
-        for t in grads:   # in place, skipped on the device when the upstream scalar is exactly 1
-            check(lib.ys_scale_inplace(ptr(t), t.numel(), ptr(g), stream_ptr(t.device)), "ys_scale_inplace")
+        with _lib.on_device(*grads, g):
+            for t in grads:   # in place, skipped on the device when the upstream scalar is exactly 1
+                check(lib.ys_scale_inplace(ptr(t), t.numel(), ptr(g), stream_ptr(t.device)), "ys_scale_inplace")
         ctx.grads = None
+        ctx.consumed = True
         return (None, None, None, None, None) + tuple(grads)
 
 

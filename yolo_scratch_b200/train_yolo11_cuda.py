@@ -1,5 +1,7 @@
 """Drop-in for the NMS / decode-for-metrics functions of the reference's train script
-(train_yolo11_cuda.py:265-437): same names, arguments and return types, on the B200 kernels.
+(train_yolo11_cuda.py:265-437): same names, arguments and return types, on the B200 kernels
+(two optional, non-reference keyword arguments are added: `labels=` on nms_simple and `class_aware=` on
+decode_predictions_for_metrics; with their defaults the behaviour is the reference's).
 
     decode_predictions_for_metrics(preds, img_size, conf_threshold, iou_threshold, device) -> list[dict]
     nms_simple(boxes, scores, iou_threshold) -> list[int]
@@ -36,9 +38,10 @@ def nms_batched(pred, conf_threshold, iou_threshold, img_size, class_aware=False
     kl = torch.empty(B, A, device=dev, dtype=torch.int32)
     kc = torch.empty(B, device=dev, dtype=torch.int32)
     ws = _ws.get(lib.ys_nms_workspace_bytes(B, A), dev)
-    check(lib.ys_nms_batched(ptr(p), layout, B, A, nc, float(conf_threshold), float(iou_threshold), float(img_size),
-                             int(bool(class_aware)), ptr(ka), ptr(kb), ptr(ks), ptr(kl), ptr(kc), ptr(ws), ws.numel(),
-                             stream_ptr(dev)), "ys_nms_batched")
+    with _lib.on_device(p):
+        check(lib.ys_nms_batched(ptr(p), layout, B, A, nc, float(conf_threshold), float(iou_threshold), float(img_size),
+                                 int(bool(class_aware)), ptr(ka), ptr(kb), ptr(ks), ptr(kl), ptr(kc), ptr(ws), ws.numel(),
+                                 stream_ptr(dev)), "ys_nms_batched")
     return ka, kb, ks, kl, kc
 
 
@@ -73,19 +76,21 @@ def nms_simple(boxes, scores, iou_threshold, labels=None):
     keep = torch.empty(N, device=dev, dtype=torch.int32)
     cnt = torch.empty(1, device=dev, dtype=torch.int32)
     ws = _ws.get(lib.ys_nms_workspace_bytes(1, N), dev)
-    check(lib.ys_nms_single(ptr(b), ptr(s), ptr(l), N, float(iou_threshold), ptr(keep), ptr(cnt), ptr(ws), ws.numel(),
-                            stream_ptr(dev)), "ys_nms_single")
+    with _lib.on_device(b, s, l):
+        check(lib.ys_nms_single(ptr(b), ptr(s), ptr(l), N, float(iou_threshold), ptr(keep), ptr(cnt), ptr(ws), ws.numel(),
+                                stream_ptr(dev)), "ys_nms_single")
     return keep[: int(cnt.item())].tolist()
 
 
 def calculate_iou_batch_simple(boxes1, boxes2):
-    """Reference train_yolo11_cuda.py:402-437: (1,4)|(N,4) x (M,4) -> (M,) if N == 1 else (N,M)."""
+    """Reference train_yolo11_cuda.py:402-437: (1,4)|(N,4) x (M,4) -> (N,M), squeezed when N == 1."""
     if boxes1.dim() == 1:
         boxes1 = boxes1.unsqueeze(0)
     _lib.require_cuda(boxes1, "boxes1")
     b1 = boxes1.detach().float().contiguous()
     b2 = boxes2.detach().float().contiguous().view(-1, 4)
     out = torch.empty(b1.shape[0], b2.shape[0], device=b1.device, dtype=torch.float32)
-    check(_lib.lib().ys_pairwise_iou(ptr(b1), b1.shape[0], ptr(b2), b2.shape[0], 0, ptr(out), stream_ptr(b1.device)),
-          "ys_pairwise_iou")
-    return out.squeeze(0) if out.shape[0] == 1 else out
+    with _lib.on_device(b1, b2):
+        check(_lib.lib().ys_pairwise_iou(ptr(b1), b1.shape[0], ptr(b2), b2.shape[0], 0, ptr(out), stream_ptr(b1.device)),
+              "ys_pairwise_iou")
+    return out.squeeze() if out.shape[0] == 1 else out      # `iou.squeeze()` (:437): (1,M) -> (M,), (1,1) -> 0-dim

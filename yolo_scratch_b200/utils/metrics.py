@@ -15,8 +15,9 @@ def calculate_iou_batch(boxes1, boxes2):
     b1 = boxes1.detach().float().contiguous().view(-1, 4)
     b2 = boxes2.detach().float().contiguous().view(-1, 4)
     out = torch.empty(b1.shape[0], b2.shape[0], device=b1.device, dtype=torch.float32)
-    check(_lib.lib().ys_pairwise_iou(ptr(b1), b1.shape[0], ptr(b2), b2.shape[0], 0, ptr(out), stream_ptr(b1.device)),
-          "ys_pairwise_iou")
+    with _lib.on_device(b1, b2):
+        check(_lib.lib().ys_pairwise_iou(ptr(b1), b1.shape[0], ptr(b2), b2.shape[0], 0, ptr(out), stream_ptr(b1.device)),
+              "ys_pairwise_iou")
     return out
 
 
@@ -90,9 +91,10 @@ def match_detections(predictions, targets, conf_threshold, iou_thresholds):
     thr = (C.c_double * T)(*[float(x) for x in iou_thresholds])
     tp = torch.zeros(B, P, T, dtype=torch.uint8, device=dev)
     nv = torch.zeros(B, dtype=torch.int32, device=dev)
-    check(_lib.lib().ys_match_detections(ptr(pb), ptr(ps.contiguous()), ptr(pc), B, P, ptr(gt), ptr(off), max(counts + [0]),
-                                         float(conf_threshold), thr, T, ptr(tp), ptr(nv), stream_ptr(dev)),
-          "ys_match_detections")
+    with _lib.on_device(pb, gt):
+        check(_lib.lib().ys_match_detections(ptr(pb), ptr(ps.contiguous()), ptr(pc), B, P, ptr(gt), ptr(off), max(counts + [0]),
+                                             float(conf_threshold), thr, T, ptr(tp), ptr(nv), stream_ptr(dev)),
+              "ys_match_detections")
     return tp.cpu().numpy(), ps.cpu().numpy(), nv.cpu().numpy(), int(sum(counts))
 
 
@@ -145,8 +147,9 @@ def cda_nms(predictions, max_detections=10, dga_thresh=0.15):
     cnt = torch.tensor([n], dtype=torch.int32, device=dev)
     keep = torch.zeros(1, max_detections, dtype=torch.int32, device=dev)
     kc = torch.zeros(1, dtype=torch.int32, device=dev)
-    check(_lib.lib().ys_cda_nms(ptr(sb), ptr(sa) if sa is not None else None, ptr(cnt), 1, n, int(max_detections),
-                                float(dga_thresh), ptr(keep), ptr(kc), stream_ptr(dev)), "ys_cda_nms")
+    with _lib.on_device(sb, sa):
+        check(_lib.lib().ys_cda_nms(ptr(sb), ptr(sa) if sa is not None else None, ptr(cnt), 1, n, int(max_detections),
+                                    float(dga_thresh), ptr(keep), ptr(kc), stream_ptr(dev)), "ys_cda_nms")
     kept = order[keep[0, :int(kc.item())].long()]
     out = {"boxes": boxes[kept], "scores": scores[kept],
            "angles": angles[kept] if angles is not None else torch.zeros(len(kept), device=dev)}
