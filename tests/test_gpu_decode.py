@@ -41,3 +41,29 @@ def test_detect_inference_640_then_nms_end_to_end(cuda_lib):
         xyxy, sc, cl, src = c_oracle.filter_candidates(yc[b], 0.25)
         keep = c_oracle.nms(xyxy, sc, 0.45)
         assert np.array_equal(ka[b, :int(kc[b])].cpu().numpy(), src[keep])
+
+
+@pytest.mark.parametrize("shapes,nc", [
+    ([(84, 84), (42, 42), (21, 21)], 80),      # imgsz 672: P5 = 441 = 1 mod 4
+    ([(9, 7), (5, 3), (3, 1)], 5),             # every level unaligned
+    ([(20, 28), (10, 14), (5, 7)], 6),         # non-square head, 35 = 3 mod 4
+])
+def test_detect_inference_unaligned_levels(cuda_lib, shapes, nc):
+    """Head shapes the float4 kernel cannot take (the reference's Detect.inference accepts any image size,
+    models/yolo11_modules.py:248-266): the any-shape kernel, both output layouts, against the oracle port."""
+    from oracle import ref_port as orc
+    from yolo_scratch_b200.head_decode import detect_inference
+    feats = synth.make_head_levels(2, 0, nc, 16, seed=410, shapes=shapes)
+    ref = orc.detect_inference(feats, nc, 16, synth.LEVEL_STRIDES)
+    dev = [f.cuda() for f in feats]
+    y = detect_inference(dev, nc)
+    scale = float(shapes[0][0] * 8)
+    assert y.shape == ref.shape
+    assert torch.allclose(y.cpu()[:, :4], ref[:, :4], rtol=2e-6, atol=1e-6 * scale)
+    assert torch.allclose(y.cpu()[:, 4:], ref[:, 4:], rtol=2e-6, atol=1e-7)
+    y2 = detect_inference(dev, nc, anchor_major=True)
+    assert torch.equal(y2.permute(0, 2, 1).contiguous(), y)
+    # a batch slice whose data pointer is not 16-byte aligned (contiguous view into a larger tensor)
+    if (feats[2].shape[1] * feats[2].shape[2] * feats[2].shape[3]) % 4:
+        y3 = detect_inference([f[1:] for f in dev], nc)
+        assert torch.equal(y3, y[1:])

@@ -335,7 +335,7 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     const int b = (FUSED && io.img_order && !early) ? io.img_order[blockIdx.y] : (int)blockIdx.y;
     // fused: blocks are cut per level (a block never straddles two levels: one tensor operation loads its tile)
     int lvl = 0, i_lvl = 0, a;
-    bool live, warp_cols = false;
+    bool live, warp_cols = false, use_tma = false;
     if (FUSED) {
 #pragma unroll
         for (int k = 1; k < YS_MAX_LEVELS; ++k)
@@ -346,7 +346,8 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         a = L.a_off[lvl] + i_lvl;
         // each warp feeds itself: lane 0 starts the first kScanStages sides of the warp's 32 anchors
         warp_cols = i0 + 32 * warp < L.hw[lvl];
-        if (lane == 0 && warp_cols) {
+        use_tma = L.tma[lvl] != 0;      // rows of this level 16-byte aligned: side tiles by TMA; else plain loads below
+        if (lane == 0 && warp_cols && use_tma) {
 #pragma unroll
             for (int s = 0; s < kScanStages; ++s) {
                 const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_mbar[warp][s]);
@@ -395,7 +396,21 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     float ax = 0.f, ay = 0.f;
     if (FUSED) {
         float d[4] = {0.f, 0.f, 0.f, 0.f};
-        if (warp_cols) {
+        if (warp_cols && !use_tma) {
+            // plain-load loader (h*w % 4 != 0 or unaligned base: no tensor map over this level): lane = anchor, every
+            // channel row piece of the warp is one contiguous 128-byte run
+            const float *xs = L.x[lvl] + (size_t)b * L.C * L.hw[lvl] + i_lvl;
+            const size_t hw = (size_t)L.hw[lvl];
+#pragma unroll 1
+            for (int s = 0; s < 4; ++s) {
+                float z[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) z[j] = live ? __ldg(xs + (size_t)(16 * s + j) * hw) : 0.f;
+                float m2, inv_s;
+                const float v = dfl_stats16(z, m2, inv_s);
+                d[0] = s == 0 ? v : d[0]; d[1] = s == 1 ? v : d[1]; d[2] = s == 2 ? v : d[2]; d[3] = s == 3 ? v : d[3];
+            }
+        } else if (warp_cols) {
             const int i0 = i_lvl - tid;
 #pragma unroll
             for (int s = 0; s < 4; ++s) {

@@ -1,6 +1,7 @@
 // ys_decode.cu -- inference decode (DFL + dist2bbox + sigmoid) and the IoU utility entry points.
 // Replaces models/yolo11_modules.py:180-192, :248-266, :303-312, utils/metrics.py:49-81,
 // train_yolo11_cuda.py:402-437 and the forward of losses/yolo_v8_loss.py:12-61; see include/ys_b200.h.
+#include <string.h>
 #include "ys_assign.cuh"
 
 namespace ys {
@@ -99,6 +100,66 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer(LevelSet L, int nc
     }
 }
 
+// The same decode for head shapes the vector kernel cannot take (a level with h*w % 4 != 0, or pointers that are not
+// 16-byte aligned -- the reference accepts any image size, models/yolo11_modules.py:248-266): thread = one anchor, every
+// load and store of a warp is a contiguous run of 4-byte elements.  Block = 128 consecutive anchors of one level.
+template <int LAYOUT>
+__global__ void __launch_bounds__(kDecThreads) k_decode_infer_any(LevelSet L, int nc, float *__restrict__ out) {
+    extern __shared__ float s_out[];           // LAYOUT 1: [kChunk][R] staging
+    const int b = blockIdx.y, chunk = blockIdx.x;
+    const int tid = threadIdx.x;
+    int l = 0;
+#pragma unroll
+    for (int k = 1; k < YS_MAX_LEVELS; ++k)
+        if (k < L.n && chunk >= L.chunk_off[k]) l = k;
+    const int hw = L.hw[l], w = L.w[l];
+    const float st = L.stride[l];
+    const int c0 = (chunk - L.chunk_off[l]) * kChunk;
+    const int i = c0 + tid;
+    const bool live = i < hw;
+    const int R = 4 + nc;
+    const int A = L.A_true;
+    const int a = L.a_true_off[l] + i;
+    if (live) {
+        const float *xin = L.x[l] + (size_t)b * L.C * hw + i;
+        float dm[4];
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            float z[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) z[j] = __ldg(xin + (size_t)(s * 16 + j) * hw);
+            float m2, inv_s;
+            dm[s] = dfl_stats16(z, m2, inv_s);
+        }
+        const int iy = i / w, ix = i - iy * w;
+        const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
+        const float x1 = gx - dm[0], y1 = gy - dm[1], x2 = gx + dm[2], y2 = gy + dm[3];
+        float o[4];
+        o[0] = (x1 + x2) / 2 * st;      // dist2bbox(xywh=True) * strides  (models/yolo11_modules.py:263, :309-311)
+        o[1] = (y1 + y2) / 2 * st;
+        o[2] = (x2 - x1) * st;
+        o[3] = (y2 - y1) * st;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            if (LAYOUT == 0) out[((size_t)b * R + c) * A + a] = o[c];
+            else s_out[(size_t)tid * R + c] = o[c];
+        }
+        const float *xc = xin + (size_t)64 * hw;
+        for (int c = 0; c < nc; ++c) {
+            const float sg = sigmoidf(__ldg(xc + (size_t)c * hw));
+            if (LAYOUT == 0) out[((size_t)b * R + 4 + c) * A + a] = sg;
+            else s_out[(size_t)tid * R + 4 + c] = sg;
+        }
+    }
+    if (LAYOUT == 1) {
+        __syncthreads();
+        const int rows = min(kChunk, hw - c0);
+        float *dst = out + ((size_t)b * A + L.a_true_off[l] + c0) * R;
+        const int total = rows * R;
+        for (int k = tid; k < total; k += kDecThreads) dst[k] = s_out[k];
+    }
+}
+
 __global__ void k_pairwise_iou(const float4 *__restrict__ b1, int N, const float4 *__restrict__ b2, int M, int kind,
                                float *__restrict__ out) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -173,25 +234,29 @@ using namespace ys;
 
 // build_levels lives in ys_loss.cu; re-declare a light version here for the decode entry point
 static int build_levels_dec(LevelSet &L, int n_levels, const float *const *xs, const int *hs, const int *ws,
-                            const float *strides, int nc, int reg_max) {
+                            const float *strides, int nc, int reg_max, bool &all_vec) {
     YS_REQUIRE(n_levels >= 1 && n_levels <= YS_MAX_LEVELS, YS_ERR_BAD_ARG, "n_levels must be in [1,%d]", YS_MAX_LEVELS);
     YS_REQUIRE(reg_max == 16, YS_ERR_UNSUPPORTED, "reg_max must be 16");
     YS_REQUIRE(nc >= 1, YS_ERR_BAD_ARG, "nc must be >= 1");
+    memset(&L, 0, sizeof(L));
     L.n = n_levels;
     L.C = 4 * reg_max + nc;
     int a = 0, ch = 0;
+    all_vec = true;
     for (int i = 0; i < n_levels; ++i) {
         YS_REQUIRE(xs[i] != nullptr && hs[i] > 0 && ws[i] > 0, YS_ERR_BAD_ARG, "level %d: null pointer or empty shape", i);
-        YS_REQUIRE(((uintptr_t)xs[i] & 15) == 0, YS_ERR_BAD_ARG, "level %d: pointer must be 16-byte aligned", i);
-        YS_REQUIRE((hs[i] * ws[i]) % 4 == 0, YS_ERR_UNSUPPORTED, "level %d: h*w must be a multiple of 4", i);
+        YS_REQUIRE(((uintptr_t)xs[i] & 3) == 0, YS_ERR_BAD_ARG, "level %d: pointer must be 4-byte aligned", i);
         L.x[i] = xs[i]; L.g[i] = nullptr; L.w[i] = ws[i]; L.hw[i] = hs[i] * ws[i]; L.stride[i] = strides[i];
-        L.a_off[i] = a; L.chunk_off[i] = ch;
+        L.tma[i] = (L.hw[i] % 4 == 0) && (((uintptr_t)xs[i] & 15) == 0);
+        all_vec = all_vec && L.tma[i];
+        L.a_off[i] = a; L.a_true_off[i] = a; L.chunk_off[i] = ch;      // the decode writes the reference's dense numbering only
         a += L.hw[i];
         ch += (L.hw[i] + kChunk - 1) / kChunk;
     }
-    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.chunk_off[i] = ch; }
-    for (int i = n_levels; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; }
+    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.a_true_off[i] = a; L.chunk_off[i] = ch; }
+    for (int i = n_levels; i < YS_MAX_LEVELS; ++i) { L.w[i] = 1; L.stride[i] = 1.f; }
     L.A = a;
+    L.A_true = a;
     L.n_chunks = ch;
     return YS_OK;
 }
@@ -204,17 +269,24 @@ extern "C" int ys_decode_infer(int n_levels, const float *const *level_x_host, c
     YS_REQUIRE(B >= 1 && B <= 65535, YS_ERR_BAD_ARG, "B must be in [1,65535]");
     YS_REQUIRE(layout == 0 || layout == 1, YS_ERR_BAD_ARG, "layout must be 0 or 1");
     LevelSet L;
-    int rc = build_levels_dec(L, n_levels, level_x_host, level_h_host, level_w_host, level_stride_host, nc, reg_max);
+    bool all_vec = true;
+    int rc = build_levels_dec(L, n_levels, level_x_host, level_h_host, level_w_host, level_stride_host, nc, reg_max, all_vec);
     if (rc) return rc;
     dim3 grid(L.n_chunks, B);
+    const size_t smem = layout == 1 ? (size_t)kChunk * (4 + nc) * sizeof(float) : 0;
+    YS_REQUIRE(smem <= 200 * 1024, YS_ERR_UNSUPPORTED, "nc too large for the staged layout (%d)", nc);
+    // float4 kernel when every level's rows (and, for the channels-first output, every output row) are 16-byte aligned
+    const bool vec = all_vec && (layout == 1 || L.A % 4 == 0);
     if (layout == 0) {
-        k_decode_infer<0><<<grid, kDecThreads, 0, stream>>>(L, nc, out);
+        if (vec) k_decode_infer<0><<<grid, kDecThreads, 0, stream>>>(L, nc, out);
+        else k_decode_infer_any<0><<<grid, kDecThreads, 0, stream>>>(L, nc, out);
     } else {
-        const size_t smem = (size_t)kChunk * (4 + nc) * sizeof(float);
-        YS_REQUIRE(smem <= 200 * 1024, YS_ERR_UNSUPPORTED, "nc too large for the staged layout (%d)", nc);
-        static thread_local bool attr_set = false;
-        if (!attr_set) { cudaFuncSetAttribute(k_decode_infer<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr_set = true; }
-        k_decode_infer<1><<<grid, kDecThreads, smem, stream>>>(L, nc, out);
+        static DeviceOnce once_dec[2];
+        rc = optin_smem(vec ? (const void *)k_decode_infer<1> : (const void *)k_decode_infer_any<1>, 200 * 1024, once_dec[vec ? 0 : 1],
+                        "k_decode_infer");
+        if (rc) return rc;
+        if (vec) k_decode_infer<1><<<grid, kDecThreads, smem, stream>>>(L, nc, out);
+        else k_decode_infer_any<1><<<grid, kDecThreads, smem, stream>>>(L, nc, out);
     }
     YS_CHECK_LAUNCH("k_decode_infer");
     return YS_OK;

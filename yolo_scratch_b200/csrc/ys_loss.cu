@@ -341,6 +341,23 @@ __global__ void k_scale_inplace(float *__restrict__ data, size_t n, const float 
     for (; i < n; i += stride) data[i] *= s;
 }
 
+// Per-anchor state from the padded anchor space (workspace) to the reference's dense numbering (caller's buffers).
+__global__ void k_export_state(LevelSet L, int B, const float4 *__restrict__ pbox, const int *__restrict__ tgi,
+                               const float *__restrict__ norm, float4 *__restrict__ out_box, int *__restrict__ out_tgi,
+                               float *__restrict__ out_norm) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)B * L.A_true) return;
+    const int b = (int)(i / L.A_true), a = (int)(i - (size_t)b * L.A_true);
+    int l = 0;
+#pragma unroll
+    for (int k = 1; k < YS_MAX_LEVELS; ++k)
+        if (k < L.n && a >= L.a_true_off[k]) l = k;
+    const size_t src = (size_t)b * L.A + L.a_off[l] + (a - L.a_true_off[l]);
+    if (out_box) out_box[i] = pbox[src];
+    if (out_tgi) out_tgi[i] = tgi[src];
+    if (out_norm) out_norm[i] = norm[src];
+}
+
 // Dense assigner outputs (losses/yolo_v8_loss.py:246-270): labels / boxes for ALL anchors (background gets
 // GT slot 0), one-hot * norm scores, bool fg, i64 gt index.
 __global__ void k_assign_emit(int B, int A, int G, int nc, const int *__restrict__ tgi, const float *__restrict__ norm,
@@ -374,33 +391,39 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
     YS_REQUIRE(nc >= 1, YS_ERR_BAD_ARG, "nc must be >= 1");
     L.n = n_levels;
     L.C = 4 * reg_max + nc;
-    int a = 0, ch = 0, sg = 0, hs16 = 0, sb = 0;
+    int a = 0, at = 0, ch = 0, hs16 = 0, sb = 0;
     for (int i = 0; i < n_levels; ++i) {
         YS_REQUIRE(xs[i] != nullptr && hs[i] > 0 && ws[i] > 0, YS_ERR_BAD_ARG, "level %d: null pointer or empty shape", i);
-        YS_REQUIRE(((uintptr_t)xs[i] & 15) == 0, YS_ERR_BAD_ARG, "level %d: pointer must be 16-byte aligned", i);
-        YS_REQUIRE((hs[i] * ws[i]) % 4 == 0, YS_ERR_UNSUPPORTED, "level %d: h*w must be a multiple of 4 (float4 path)", i);
-        L.seg_off[i] = sg;
+        YS_REQUIRE(((uintptr_t)xs[i] & 3) == 0, YS_ERR_BAD_ARG, "level %d: pointer must be 4-byte aligned", i);
+        if (gs) YS_REQUIRE(gs[i] != nullptr && ((uintptr_t)gs[i] & 3) == 0, YS_ERR_BAD_ARG, "level %d: bad grad pointer", i);
+        const int hw = hs[i] * ws[i];
+        // Any h*w is accepted (the reference only views and concatenates, losses/yolo_v8_loss.py:391-396).  Levels whose
+        // rows are 16-byte aligned take the TMA loaders and float4 stores; the others the plain-load loaders.
+        L.tma[i] = (hw % 4 == 0) && (((uintptr_t)xs[i] & 15) == 0) && (!gs || ((uintptr_t)gs[i] & 15) == 0);
+#ifdef YS_FORCE_NO_TMA       // test builds: every level through the plain-load loaders
+        L.tma[i] = 0;
+#endif
         L.hseg_off[i] = hs16;
         L.sblk_off[i] = sb;
-        sb += (hs[i] * ws[i] + kScanThreads - 1) / kScanThreads;
-        hs16 += (hs[i] * ws[i] + kBoxItem - 1) / kBoxItem;
-        sg += (hs[i] * ws[i] + kSeg - 1) / kSeg;
+        sb += (hw + kScanThreads - 1) / kScanThreads;
+        hs16 += (hw + kBoxItem - 1) / kBoxItem;
         L.x[i] = xs[i];
         L.g[i] = gs ? gs[i] : nullptr;
-        if (gs) YS_REQUIRE(gs[i] != nullptr && ((uintptr_t)gs[i] & 15) == 0, YS_ERR_BAD_ARG, "level %d: bad grad pointer", i);
         L.w[i] = ws[i];
-        L.hw[i] = hs[i] * ws[i];
+        L.hw[i] = hw;
         L.stride[i] = strides[i];
         L.a_off[i] = a;
+        L.a_true_off[i] = at;
         L.chunk_off[i] = ch;
-        a += L.hw[i];
-        ch += (L.hw[i] + kChunk - 1) / kChunk;
+        a += (hw + 3) & ~3;
+        at += hw;
+        ch += (hw + kChunk - 1) / kChunk;
     }
-    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.chunk_off[i] = ch; L.seg_off[i] = sg; L.hseg_off[i] = hs16; L.sblk_off[i] = sb; }
-    for (int i = n_levels; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; }
+    for (int i = n_levels; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = a; L.a_true_off[i] = at; L.chunk_off[i] = ch; L.hseg_off[i] = hs16; L.sblk_off[i] = sb; }
+    for (int i = n_levels; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; L.tma[i] = 0; }
     L.A = a;
+    L.A_true = at;
     L.n_chunks = ch;
-    L.n_segs = sg;
     L.n_hsegs = hs16;
     L.n_sblk = sb;
     return YS_OK;
@@ -410,22 +433,6 @@ static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-// Dynamic shared-memory opt-in of a kernel, once per device (the attribute is sticky; repeating the call on every
-// launch costs host time for nothing).  Not state that results depend on.
-template <typename K>
-static int optin_smem(K kernel, size_t bytes, unsigned long long &done_mask, const char *what) {
-    int dev = 0;
-    cudaError_t ce = cudaGetDevice(&dev);
-    YS_REQUIRE(ce == cudaSuccess, (int)ce, "%s: cudaGetDevice: %s", what, cudaGetErrorString(ce));
-    const unsigned long long bit = 1ull << (dev & 63);
-    if (done_mask & bit) return YS_OK;
-    ce = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-    YS_REQUIRE(ce == cudaSuccess, (int)ce, "%s smem opt-in: %s", what, cudaGetErrorString(ce));
-    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    done_mask |= bit;
-    return YS_OK;
-}
-
 // Launch with programmatic dependent launch (PDL): the kernel may start while its predecessor in the stream is still
 // draining (the predecessor calls cudaTriggerProgrammaticLaunchCompletion() at its start, i.e. the dependent becomes
 // eligible once the predecessor's last wave is resident); the dependent runs its prologue and then blocks in
@@ -443,7 +450,8 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 }
 
 static int get_encoder(EncodeTiledFn &out) {
-    static EncodeTiledFn encode = nullptr;
+    static std::atomic<EncodeTiledFn> cached{nullptr};      // a process-wide driver entry point, not per-call state
+    EncodeTiledFn encode = cached.load(std::memory_order_acquire);
     if (!encode) {
         void *fn = nullptr;
         cudaDriverEntryPointQueryResult q;
@@ -451,6 +459,7 @@ static int get_encoder(EncodeTiledFn &out) {
         YS_REQUIRE(ce == cudaSuccess && fn != nullptr && q == cudaDriverEntryPointSuccess, YS_ERR_UNSUPPORTED,
                    "cuTensorMapEncodeTiled is not available from this driver");
         encode = (EncodeTiledFn)fn;
+        cached.store(encode, std::memory_order_release);
     }
     out = encode;
     return YS_OK;
@@ -461,6 +470,7 @@ static int build_scan_maps(ScanMaps &M, const LevelSet &L, int B) {
     if (rc) return rc;
     memset(&M, 0, sizeof(M));
     for (int l = 0; l < L.n; ++l) {
+        if (!L.tma[l]) continue;
         const cuuint64_t gdim[2] = {(cuuint64_t)L.hw[l], (cuuint64_t)B * (cuuint64_t)L.C};
         const cuuint64_t gstride[1] = {(cuuint64_t)L.hw[l] * 4u};
         const cuuint32_t estr[2] = {1u, 1u};
@@ -478,6 +488,7 @@ static int build_stream_maps(StreamMaps &M, const LevelSet &L, int B) {
     if (rc0) return rc0;
     memset(&M, 0, sizeof(M));
     for (int l = 0; l < L.n; ++l) {
+        if (!L.tma[l]) continue;
         const cuuint64_t gdim[2] = {(cuuint64_t)L.hw[l], (cuuint64_t)B * (cuuint64_t)L.C};
         const cuuint64_t gstride[1] = {(cuuint64_t)L.hw[l] * 4u};
         const cuuint32_t estr[2] = {1u, 1u};
@@ -506,9 +517,11 @@ struct LossWorkspace {
 };
 
 static inline int scan_blocks(int A) { return (A + kScanThreads - 1) / kScanThreads + YS_MAX_LEVELS; }   // upper bound (per-level cut)
-static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, int n_gt, int nc) {
+// A = anchors per image as the caller counts them; per-anchor arrays are sized for the padded index space
+static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A_true, int n_gt, int nc) {
     Carver c(base, cap);
     const size_t N = (size_t)(n_gt > 0 ? n_gt : 1);
+    const size_t A = (size_t)padded_anchor_bound(A_true);
     W.counters = c.take<unsigned>((size_t)B + 2);
     W.tss = c.take<float>(64);
     W.gt_off = c.take<int>((size_t)B + 1);
@@ -523,7 +536,7 @@ static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A, i
     W.gt_box = c.take<float4>(N);
     W.best_key = c.take<unsigned long long>(N);
     W.img_sum = c.take<double>((size_t)B);
-    W.scan_partial = c.take<float>((size_t)B * scan_blocks(A));
+    W.scan_partial = c.take<float>((size_t)B * scan_blocks((int)A));
     W.tgi = c.take<int>((size_t)B * A);
     W.lab = c.take<int>((size_t)B * A);
     W.norm = c.take<float>((size_t)B * A);
@@ -560,7 +573,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     int rc = build_levels(L, n_levels, level_x_host, level_grad_host, level_h_host, level_w_host, level_stride_host, nc, reg_max);
     if (rc) return rc;
     LossWorkspace W;
-    carve_loss(W, workspace, workspace_bytes, B, L.A, n_gt, nc);
+    carve_loss(W, workspace, workspace_bytes, B, L.A_true, n_gt, nc);
     YS_REQUIRE(W.bytes <= workspace_bytes, YS_ERR_WORKSPACE, "workspace too small: need %zu, got %zu", W.bytes, workspace_bytes);
     YS_REQUIRE(((uintptr_t)workspace & 255) == 0, YS_ERR_BAD_ARG, "workspace must be 256-byte aligned");
     if (pred_boxes_px) { YS_REQUIRE(((uintptr_t)pred_boxes_px & 15) == 0, YS_ERR_BAD_ARG, "pred_boxes_px must be 16-byte aligned"); }
@@ -574,14 +587,11 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
 #define YS_IDENTITY_WAVE YS_SCAN_MINBLOCKS      // resident k_assign blocks per SM
 #endif
     int n_identity = 0;
+    int sms = 0;
+    rc = device_sm_count(sms);
+    if (rc) return rc;
     {
-        static int s_sms = 0;
-        if (s_sms == 0) {
-            int dev = 0;
-            if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&s_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || s_sms <= 0)
-                s_sms = 148;
-        }
-        const int wave = YS_IDENTITY_WAVE * s_sms;
+        const int wave = YS_IDENTITY_WAVE * sms;
         n_identity = (wave + L.n_sblk - 1) / L.n_sblk;
         if (n_identity > B) n_identity = B;
 #ifdef YS_NO_EARLY       // experiment: every block waits for k_pack_gt first
@@ -614,10 +624,13 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     // stream, the producer of the head outputs included, has completed before it starts)
     io.n_identity = (stages & YS_STAGE_PACK) ? (io.img_order ? n_identity : B) : 0;
     io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
-    io.pbox = pred_boxes_px ? (float4 *)pred_boxes_px : W.pbox;
-    io.tgi = target_gt_idx ? (int *)target_gt_idx : W.tgi;
+    // optional exports: written in place when the padded anchor space is the reference's (every h*w % 4 == 0), else
+    // kept in the workspace and remapped by k_export_state after the assignment
+    const bool remap = L.A != L.A_true;
+    io.pbox = (pred_boxes_px && !remap) ? (float4 *)pred_boxes_px : W.pbox;
+    io.tgi = (target_gt_idx && !remap) ? (int *)target_gt_idx : W.tgi;
     io.lab = W.lab;
-    io.norm = norm_out ? norm_out : W.norm;
+    io.norm = (norm_out && !remap) ? norm_out : W.norm;
     io.partial = W.scan_partial; io.img_sum = W.img_sum; io.tss = W.tss;
     io.done_counter = W.counters; io.img_done = W.counters + 2;
     io.nc = nc; io.alpha = alpha; io.beta = beta; io.eps = 1e-9f;
@@ -627,13 +640,19 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         rc = build_scan_maps(SM, L, B);
         if (rc) return rc;
         const size_t smem = (size_t)kScanTileBytes + sizeof(AssignSmem);
-        static unsigned long long optin_assign = 0ull;
-        rc = optin_smem(k_assign<true>, smem, optin_assign, "k_assign");
+        static DeviceOnce optin_assign;
+        rc = optin_smem((const void *)k_assign<true>, smem, optin_assign, "k_assign");
         if (rc) return rc;
         dim3 gs(L.n_sblk, B);
         cudaError_t le = launch_pdl(k_assign<true>, gs, dim3(kScanThreads), smem, stream, L, io, B, SM);
         YS_REQUIRE(le == cudaSuccess, (int)le, "k_assign launch: %s", cudaGetErrorString(le));
         YS_CHECK_LAUNCH("k_assign");
+        if (remap && (pred_boxes_px || target_gt_idx || norm_out)) {
+            const size_t tot = (size_t)B * L.A_true;
+            k_export_state<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(L, B, W.pbox, W.tgi, W.norm, (float4 *)pred_boxes_px,
+                                                                             (int *)target_gt_idx, norm_out);
+            YS_CHECK_LAUNCH("k_export_state");
+        }
     }
 
     if (stages & YS_STAGE_LOSS) {
@@ -647,10 +666,6 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         YS_REQUIRE((long long)B * P.items_per_img < 2147483647LL / 2, YS_ERR_UNSUPPORTED, "too many work items");
         P.total_items = B * P.items_per_img;
         P.hyp_box = hyp_box; P.hyp_cls = hyp_cls; P.hyp_dfl = hyp_dfl; P.batch = (float)B;
-        int dev = 0, sms = 0;
-        cudaError_t ce = cudaGetDevice(&dev);
-        if (ce == cudaSuccess) ce = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        YS_REQUIRE(ce == cudaSuccess && sms > 0, (int)(ce ? ce : cudaErrorUnknown), "cannot query the SM count: %s", cudaGetErrorString(ce));
         const int want = (P.total_items + kStreamWarps - 1) / kStreamWarps;
         const unsigned blocks = (unsigned)(want < sms ? (want > 0 ? want : 1) : (sms > 4096 ? 4096 : sms));
         // Ring depth: two stages where most box items are all-background (their neighbours in time are cheap and the SMs'
@@ -683,19 +698,14 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         StreamMaps M;
         rc = build_stream_maps(M, L, B);
         if (rc) return rc;
-        static unsigned long long optin_t[2] = {0ull, 0ull}, optin_f[2] = {0ull, 0ull};
-        cudaError_t le;
-        if (level_grad_host) {
-            rc = deep ? optin_smem(k_loss_stream<true, 3>, smem, optin_t[1], "k_loss_stream") : optin_smem(k_loss_stream<true, 2>, smem, optin_t[0], "k_loss_stream");
-            if (rc) return rc;
-            le = deep ? launch_pdl(k_loss_stream<true, 3>, dim3(blocks), dim3(kStreamThreads), smem, stream, L, P, M)
-                      : launch_pdl(k_loss_stream<true, 2>, dim3(blocks), dim3(kStreamThreads), smem, stream, L, P, M);
-        } else {
-            rc = deep ? optin_smem(k_loss_stream<false, 3>, smem, optin_f[1], "k_loss_stream(fwd)") : optin_smem(k_loss_stream<false, 2>, smem, optin_f[0], "k_loss_stream(fwd)");
-            if (rc) return rc;
-            le = deep ? launch_pdl(k_loss_stream<false, 3>, dim3(blocks), dim3(kStreamThreads), smem, stream, L, P, M)
-                      : launch_pdl(k_loss_stream<false, 2>, dim3(blocks), dim3(kStreamThreads), smem, stream, L, P, M);
-        }
+        static DeviceOnce optin_ls[4];
+        typedef void (*StreamKernel)(LevelSet, StreamParams, const StreamMaps);
+        const int kid = (level_grad_host ? 0 : 2) + (deep ? 1 : 0);
+        const StreamKernel kern = level_grad_host ? (deep ? (StreamKernel)k_loss_stream<true, 3> : (StreamKernel)k_loss_stream<true, 2>)
+                                                  : (deep ? (StreamKernel)k_loss_stream<false, 3> : (StreamKernel)k_loss_stream<false, 2>);
+        rc = optin_smem((const void *)kern, smem, optin_ls[kid], "k_loss_stream");
+        if (rc) return rc;
+        cudaError_t le = launch_pdl(kern, dim3(blocks), dim3(kStreamThreads), smem, stream, L, P, M);
         YS_REQUIRE(le == cudaSuccess, (int)le, "k_loss_stream launch: %s", cudaGetErrorString(le));
         YS_CHECK_LAUNCH("k_loss_stream");
     }
@@ -768,10 +778,10 @@ extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, co
     cudaMemsetAsync(workspace, 0, W.zero_bytes, stream);
 
     LevelSet L;
-    L.n = 1; L.A = A; L.C = nc; L.n_chunks = 0;
-    for (int i = 0; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; }
-    for (int i = 0; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = i == 0 ? 0 : A; L.chunk_off[i] = 0; L.seg_off[i] = 0; L.hseg_off[i] = 0; L.sblk_off[i] = 0; }
-    L.n_segs = 0; L.n_hsegs = 0; L.n_sblk = 0;
+    L.n = 1; L.A = A; L.A_true = A; L.C = nc; L.n_chunks = 0;      // dense entry point: one index space, no levels
+    for (int i = 0; i < YS_MAX_LEVELS; ++i) { L.x[i] = nullptr; L.g[i] = nullptr; L.w[i] = 1; L.hw[i] = 0; L.stride[i] = 1.f; L.tma[i] = 0; }
+    for (int i = 0; i <= YS_MAX_LEVELS; ++i) { L.a_off[i] = i == 0 ? 0 : A; L.a_true_off[i] = L.a_off[i]; L.chunk_off[i] = 0; L.hseg_off[i] = 0; L.sblk_off[i] = 0; }
+    L.n_hsegs = 0; L.n_sblk = 0;
 
     AssignIO io;
     io.gt_off = nullptr; io.G = G; io.gt_box = (const float4 *)gt_bboxes; io.gt_label_i = nullptr;

@@ -163,42 +163,84 @@ __device__ __forceinline__ Item unpack_item(const LevelSet &L, const ItemQ &q) {
     return it;
 }
 
-// Issue the bulk copies of one item into a stage (whole warp calls; lanes issue one or two rows each).
-// Returns nothing; the stage's mbarrier completes when all bytes have landed.  Box items: only when has_fg.
+// Issue the asynchronous copies of one item into a stage (lane 0 issues; the stage's mbarrier completes when all bytes
+// have landed).  Box items: only when the item has a foreground anchor.  The per-anchor state always travels by bulk copy
+// (the padded anchor space keeps every item's first entry 16-byte aligned; counts are rounded up to 4 entries, which
+// stays inside the level's padding).  The head-value tile comes by ONE tensor operation when the level has a tensor map
+// (L.tma); otherwise the consuming warp fills it with plain loads right after the wait (fill_tile_plain).
 __device__ __forceinline__ void issue_item(const LevelSet &L, const StreamParams &P, const StreamMaps &M, const Item &it,
                                            char *stage, unsigned bar, int lane) {
     const unsigned tile = smem_u32(stage), aux = tile + kTileFloats * 4;
     const size_t arow = (size_t)it.b * L.A + L.a_off[it.l] + it.i0;
-    const unsigned rb = (unsigned)it.n_live * 4u;
-    // the tensor operation always delivers the full 4 KB box (columns past the level's end arrive as zeros)
+    const unsigned n4 = (unsigned)((it.n_live + 3) & ~3);
+    const unsigned rb = n4 * 4u;
+    const bool tma = L.tma[it.l] != 0;
+    // the tensor operation always delivers the full box (columns past the level's end arrive as zeros)
     if (it.group < 0) {
         if (lane == 0) {
-            mbar_expect_tx(bar, 4096u + (unsigned)it.n_live * 20u);                   // tile + pbox (16 B) + norm (4 B)
-            tma_g2s_2d(tile, &M.box[it.l], it.i0, it.b * L.C, bar);
+            mbar_expect_tx(bar, (tma ? 4096u : 0u) + (unsigned)it.n_live * 16u + rb);         // tile + pbox (16 B) + norm (4 B)
+            if (tma) tma_g2s_2d(tile, &M.box[it.l], it.i0, it.b * L.C, bar);
             bulk_g2s(aux, P.pbox + arow, (unsigned)it.n_live * 16u, bar);
             bulk_g2s(aux + 256u, P.norm + arow, rb, bar);
         }
     } else {
         if (lane == 0) {
-            mbar_expect_tx(bar, (unsigned)(kClsRows * 512) + 2u * rb);
-            tma_g2s_2d(tile, &M.cls[it.l], it.i0, it.b * L.C + 64 + it.group * kClsRows, bar);
+            mbar_expect_tx(bar, (tma ? (unsigned)(kClsRows * 512) : 0u) + 2u * rb);
+            if (tma) tma_g2s_2d(tile, &M.cls[it.l], it.i0, it.b * L.C + 64 + it.group * kClsRows, bar);
             bulk_g2s(aux, P.lab + arow, rb, bar);
             bulk_g2s(aux + 512u, P.norm + arow, rb, bar);
         }
     }
 }
 
+// Plain-load tile loader for levels without a tensor map (h*w % 4 != 0, or base pointers that are not 16-byte aligned):
+// the warp copies the item's rows into the stage in the layout the tensor operation would have produced -- box items
+// [64 rows][16 anchors], class items [rows][128 anchors] -- every row piece one contiguous, coalesced run; columns past
+// the level's end are written as zeros.  Ends on a __syncwarp().
+__device__ __forceinline__ void fill_tile_plain(const LevelSet &L, const StreamParams &P, const Item &it, char *stage, int lane) {
+    float *tile = reinterpret_cast<float *>(stage);
+    const size_t hw = (size_t)it.hw;
+    if (it.group < 0) {
+        const float *src = L.x[it.l] + (size_t)it.b * L.C * hw + it.i0;
+        const int a16 = lane & 15, rsub = lane >> 4;
+        const bool live = a16 < it.n_live;
+#pragma unroll 8
+        for (int r = rsub; r < 64; r += 2) tile[r * kBoxItem + a16] = live ? __ldg(src + (size_t)r * hw + a16) : 0.f;
+    } else {
+        const int c_lo = it.group * kClsRows;
+        const int c_n = min(kClsRows, P.nc - c_lo);
+        const float *src = L.x[it.l] + ((size_t)it.b * L.C + 64 + c_lo) * hw + it.i0;
+        for (int r = 0; r < c_n; ++r) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int col = lane + 32 * j;
+                tile[r * kChunk + col] = col < it.n_live ? __ldg(src + (size_t)r * hw + col) : 0.f;
+            }
+        }
+    }
+    __syncwarp();
+}
+
 // ---- box item -------------------------------------------------------------------------------------------------
 template <bool WRITE_GRAD>
 __device__ __forceinline__ void stream_box_zero(const LevelSet &L, const Item &it, int lane) {
     if (!WRITE_GRAD) return;
-    // 64 rows x 64 B: 4 lanes per row, 8 rows per instruction
     float *g = L.g[it.l] + (size_t)it.b * L.C * it.hw + it.i0;
-    const int col = (lane & 3) * 4, rsub = lane >> 2;
-    if (col < it.n_live) {
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (L.tma[it.l]) {
+        // 64 rows x 64 B: 4 lanes per row, 8 rows per instruction (h*w % 4 == 0: the 4 anchors of a piece are live together)
+        const int col = (lane & 3) * 4, rsub = lane >> 2;
+        if (col < it.n_live) {
+            const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int c = 0; c < 8; ++c) *reinterpret_cast<float4 *>(g + (size_t)(c * 8 + rsub) * it.hw + col) = z4;
+            for (int c = 0; c < 8; ++c) *reinterpret_cast<float4 *>(g + (size_t)(c * 8 + rsub) * it.hw + col) = z4;
+        }
+    } else {
+        // rows without 16-byte alignment: 16 lanes per row, 2 rows per instruction, scalar stores
+        const int col = lane & 15, rsub = lane >> 4;
+        if (col < it.n_live) {
+#pragma unroll 8
+            for (int c = 0; c < 32; ++c) g[(size_t)(c * 2 + rsub) * it.hw + col] = 0.f;
+        }
     }
 }
 
@@ -280,17 +322,35 @@ __device__ __forceinline__ void stream_box(const LevelSet &L, const StreamParams
 }
 
 // ---- class item -----------------------------------------------------------------------------------------------
-template <bool WRITE_GRAD>
+// ALIGNED (levels with 16-byte aligned rows): lane = anchors 4*lane .. 4*lane+3, one float4 per row from shared memory and
+// one float4 store per row.  Otherwise lane = anchors lane, lane+32, lane+64, lane+96: scalar shared-memory reads and
+// scalar, fully coalesced stores, each anchor live on its own.  Anchors past the level's end read a logit of -inf, which
+// contributes exactly zero to every sum (exp(-inf) = 0, max(-inf, 0) = 0) and is never stored.
+template <bool WRITE_GRAD, bool ALIGNED>
 __device__ __forceinline__ void stream_cls(const LevelSet &L, const StreamParams &P, const Item &it, const char *stage,
                                            int lane, float inv_tss, float &acc_cls) {
-    if (lane * 4 >= it.n_live) return;        // hw % 4 == 0 => the 4 anchors of a lane are live together
+    if (ALIGNED && lane * 4 >= it.n_live) return;        // h*w % 4 == 0 => the 4 anchors of a lane are live together
     const float *tile = reinterpret_cast<const float *>(stage);
     const char *aux = stage + kTileFloats * 4;
     const int c_lo = it.group * kClsRows;
     const int c_n = min(kClsRows, P.nc - c_lo);
-    const int4 lab4 = reinterpret_cast<const int4 *>(aux)[lane];
-    const float4 nr4 = reinterpret_cast<const float4 *>(aux + 512)[lane];
-    float *gc = WRITE_GRAD ? L.g[it.l] + ((size_t)it.b * L.C + 64 + c_lo) * it.hw + it.i0 + lane * 4 : nullptr;
+    // anchor j of this lane within the item
+    const int a0 = ALIGNED ? lane * 4 : lane, a1 = ALIGNED ? a0 + 1 : lane + 32, a2 = ALIGNED ? a0 + 2 : lane + 64,
+              a3 = ALIGNED ? a0 + 3 : lane + 96;
+    const bool v0 = ALIGNED || a0 < it.n_live, v1 = ALIGNED || a1 < it.n_live, v2 = ALIGNED || a2 < it.n_live,
+               v3 = ALIGNED || a3 < it.n_live;
+    int4 lab4;
+    float4 nr4;
+    if (ALIGNED) {
+        lab4 = reinterpret_cast<const int4 *>(aux)[lane];
+        nr4 = reinterpret_cast<const float4 *>(aux + 512)[lane];
+    } else {
+        const int *la = reinterpret_cast<const int *>(aux);
+        const float *na = reinterpret_cast<const float *>(aux + 512);
+        lab4 = make_int4(v0 ? la[a0] : -1, v1 ? la[a1] : -1, v2 ? la[a2] : -1, v3 ? la[a3] : -1);
+        nr4 = make_float4(v0 ? na[a0] : 0.f, v1 ? na[a1] : 0.f, v2 ? na[a2] : 0.f, v3 ? na[a3] : 0.f);
+    }
+    float *gc = WRITE_GRAD ? L.g[it.l] + ((size_t)it.b * L.C + 64 + c_lo) * it.hw + it.i0 : nullptr;
     // the class of anchor k relative to this item's first channel (never matches when background: lab = -1)
     const int r0 = lab4.x - c_lo, r1 = lab4.y - c_lo, r2 = lab4.z - c_lo, r3 = lab4.w - c_lo;
     const float gscale = P.hyp_cls * P.batch * inv_tss;
@@ -324,28 +384,39 @@ __device__ __forceinline__ void stream_cls(const LevelSet &L, const StreamParams
         o.w = elem(xv.w, S3);
         return o;
     };
+    const float ninf = __int_as_float(0xff800000);
+    auto row = [&](int c) {
+        if (ALIGNED) {
+            const float4 o = one(*reinterpret_cast<const float4 *>(tile + c * kChunk + lane * 4));
+            if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)c * it.hw + lane * 4) = o;
+        } else {
+            const float *tr = tile + c * kChunk;
+            const float4 o = one(make_float4(v0 ? tr[a0] : ninf, v1 ? tr[a1] : ninf, v2 ? tr[a2] : ninf, v3 ? tr[a3] : ninf));
+            if (WRITE_GRAD) {
+                float *gr = gc + (size_t)c * it.hw;
+                if (v0) gr[a0] = o.x;
+                if (v1) gr[a1] = o.y;
+                if (v2) gr[a2] = o.z;
+                if (v3) gr[a3] = o.w;
+            }
+        }
+    };
     if (c_n == kClsRows) {
 #pragma unroll
-        for (int c = 0; c < kClsRows; ++c) {
-            const float4 o = one(*reinterpret_cast<const float4 *>(tile + c * kChunk + lane * 4));
-            if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)c * it.hw) = o;
-        }
+        for (int c = 0; c < kClsRows; ++c) row(c);
     } else {
-        for (int c = 0; c < c_n; ++c) {
-            const float4 o = one(*reinterpret_cast<const float4 *>(tile + c * kChunk + lane * 4));
-            if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)c * it.hw) = o;
-        }
+        for (int c = 0; c < c_n; ++c) row(c);
     }
-    auto patch = [&](int r, int j, float tk) {
+    auto patch = [&](int r, int a, float tk) {
         if (r >= 0 && r < c_n) {
-            const float x = tile[r * kChunk + lane * 4 + j];
+            const float x = tile[r * kChunk + a];
             float e;
             const float sg = sig_e(x, e);
             xt = fmaf(x, tk, xt);
-            if (WRITE_GRAD) gc[(size_t)r * it.hw + j] = fmaf(sg, gscale, -tk);
+            if (WRITE_GRAD) gc[(size_t)r * it.hw + a] = fmaf(sg, gscale, -tk);
         }
     };
-    patch(r0, 0, t0); patch(r1, 1, t1); patch(r2, 2, t2); patch(r3, 3, t3);
+    patch(r0, a0, t0); patch(r1, a1, t1); patch(r2, a2, t2); patch(r3, a3, t3);
     const float S01 = fmaf(S0, S1, S0 + S1), S23 = fmaf(S2, S3, S2 + S3);
     acc_cls += pos - xt * inv_g + log1pf(fmaf(S01, S23, S01 + S23));
 }
@@ -406,6 +477,17 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, S
         return g < P.n_groups16 ? (int)(g * kStreamWarps) + warp : P.total_items;      // past the end: padding item
     };
     auto load_tg2 = [&](const Item &it) -> int { return it.n_live > 0 ? load_tg(it) : -1; };
+    // One loaded item: (levels without a tensor map: the warp fills the tile itself first,) then the item's arithmetic.
+    auto consume = [&](const Item &it, char *stage, int tg) {
+        const bool tma = L.tma[it.l] != 0;
+        if (!tma) fill_tile_plain(L, P, it, stage, lane);
+        if (it.group >= 0) {
+            if (tma) stream_cls<WRITE_GRAD, true>(L, P, it, stage, lane, inv_tss, acc_cls);
+            else stream_cls<WRITE_GRAD, false>(L, P, it, stage, lane, inv_tss, acc_cls);
+        } else {
+            stream_box<WRITE_GRAD>(L, P, it, stage, tg, lane, inv_tss, acc_box, acc_dfl);
+        }
+    };
     if (STAGES == 3) {
     // Three stages: while item k is computed, the tiles of items k+1 and k+2 are in flight and the assignment lookup of
     // k+3 is on its way.  With two stages a cheap item (an all-background box item: eight stores) left the next tile
@@ -445,13 +527,11 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, S
                 if (l2) issue_item(L, P, M, unpack_item(L, q2), ring + (size_t)s2 * kStageBytes, smem_u32(&s_bar[warp][s2]), lane);
                 if (k + 3u < my_groups) fetch(q3, t3);
             }
-            const char *stage = ring + (size_t)s * kStageBytes;
             const Item it = unpack_item(L, q0);
             if (l0) {
                 mbar_wait(smem_u32(&s_bar[warp][s]), (phase_bits >> s) & 1u);
                 phase_bits ^= 1u << s;
-                if (it.group >= 0) stream_cls<WRITE_GRAD>(L, P, it, stage, lane, inv_tss, acc_cls);
-                else stream_box<WRITE_GRAD>(L, P, it, stage, t0, lane, inv_tss, acc_box, acc_dfl);
+                consume(it, ring + (size_t)s * kStageBytes, t0);
             } else if (it.n_live > 0) {
                 stream_box_zero<WRITE_GRAD>(L, it, lane);
             }
@@ -489,12 +569,10 @@ __global__ void __launch_bounds__(kStreamThreads, 1) k_loss_stream(LevelSet L, S
             }
         }
         // ---- compute the current item
-        const char *stage = ring + (size_t)s * kStageBytes;
         if (cur_loaded) {
             mbar_wait(smem_u32(&s_bar[warp][s]), (phase_bits >> s) & 1u);
             phase_bits ^= 1u << s;
-            if (cur.group >= 0) stream_cls<WRITE_GRAD>(L, P, cur, stage, lane, inv_tss, acc_cls);
-            else stream_box<WRITE_GRAD>(L, P, cur, stage, tg_cur, lane, inv_tss, acc_box, acc_dfl);
+            consume(cur, ring + (size_t)s * kStageBytes, tg_cur);
         } else if (cur.n_live > 0) {
             stream_box_zero<WRITE_GRAD>(L, cur, lane);
         }

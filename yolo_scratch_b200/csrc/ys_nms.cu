@@ -757,13 +757,13 @@ static int run_sort_suppress(const NmsWorkspace &W, int B, int A, float iou_thr,
     int P = 1;
     while (P < A) P <<= 1;
     const size_t sort_smem = (size_t)P * sizeof(unsigned long long);
-    static thread_local bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_nms_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortMaxN * 8);
-        cudaFuncSetAttribute(k_nms_suppress<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-        cudaFuncSetAttribute(k_nms_suppress<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-        attr_set = true;
-    }
+    static DeviceOnce once_sort, once_sup[2];
+    int rc = optin_smem((const void *)k_nms_sort, kSortMaxN * 8, once_sort, "k_nms_sort");
+    if (rc) return rc;
+    rc = optin_smem((const void *)k_nms_suppress<false>, 220 * 1024, once_sup[0], "k_nms_suppress");
+    if (rc) return rc;
+    rc = optin_smem((const void *)k_nms_suppress<true>, 220 * 1024, once_sup[1], "k_nms_suppress");
+    if (rc) return rc;
     k_nms_sort<<<B, kSortThreads, sort_smem, stream>>>(W.keys, W.count, A, boxes, cls, W.sbox, W.sscore, W.scls, W.sanchor);
     YS_CHECK_LAUNCH("k_nms_sort");
     if (A <= 9 * kRegThreads) {      // register-resident columns (every 640 px / 8400-candidate case)
@@ -819,8 +819,9 @@ extern "C" int ys_nms_batched(const float *pred, int layout, int B, int A, int n
     if (layout == 1) {
         const size_t smem = (size_t)(kFilterThreads / 32) * 32 * ((4 + nc) | 1) * sizeof(float);
         YS_REQUIRE(smem <= 200 * 1024, YS_ERR_UNSUPPORTED, "nc too large for the staged filter (%d)", nc);
-        static thread_local bool attr_set = false;
-        if (!attr_set) { cudaFuncSetAttribute(k_nms_filter<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr_set = true; }
+        static DeviceOnce once_filter;
+        const int rcf = optin_smem((const void *)k_nms_filter<1>, 200 * 1024, once_filter, "k_nms_filter");
+        if (rcf) return rcf;
         k_nms_filter<1><<<blocks, kFilterThreads, smem, stream>>>(pred, B, A, nc, conf_thr, W.keys, W.boxes, W.cls, W.count);
     } else {
         k_nms_filter<0><<<blocks, kFilterThreads, 0, stream>>>(pred, B, A, nc, conf_thr, W.keys, W.boxes, W.cls, W.count);
