@@ -10,9 +10,12 @@
  * Conventions
  *  - All tensor pointers are DEVICE pointers unless the parameter name ends in
  *    _host.  Plain pointers + sizes only; no torch types.
- *  - No allocation, no host synchronisation, no global state: scratch lives in a
- *    caller-provided workspace (size from ys_*_workspace_bytes), the last
- *    argument is the cudaStream_t to launch on (as void*).
+ *  - No allocation, no host synchronisation, no state a result depends on: scratch
+ *    lives in a caller-provided workspace (size from ys_*_workspace_bytes; zero it
+ *    once after allocation), the last argument is the cudaStream_t to launch on (as
+ *    void*).  Process-wide data are limited to per-device caches held in atomics
+ *    (SM count, shared-memory opt-in done); any thread, any device.  Calls are
+ *    CUDA-graph-capturable.
  *  - Return 0 on success; YS_ERR_* (<0) for bad arguments; a positive value is a
  *    cudaError_t from a launch.  ys_last_error() gives a thread-local message.
  *  - Never throws across the ABI.  Re-entrant across streams as long as each
@@ -49,7 +52,9 @@ int ys_device_info(int *sm_count, int *cc_major, int *cc_minor);
  * TaskAlignedAssigner.forward (:78-180) and BboxLoss.forward (:280-324), plus
  * the autograd backward of all of it (train_yolo11_cuda.py:57 loss.backward()).
  *
- *  level_x_host[n_levels]    device pointers to the NCHW head outputs (B, 4*reg_max+nc, h, w), fp32, contiguous
+ *  level_x_host[n_levels]    device pointers to the NCHW head outputs (B, 4*reg_max+nc, h, w), fp32, contiguous;
+ *                            any h, w (levels with h*w % 4 != 0 or a base pointer that is not 16-byte aligned take
+ *                            plain-load tile loaders instead of TMA)
  *  level_grad_host[n_levels] device pointers to same-shaped gradient buffers, or NULL => forward only
  *  level_h/w/stride_host     per-level sizes and strides (host arrays)
  *  batch_idx (N) i64, cls (N) i64, bboxes (N,4) fp32 normalised xyxy: the flat GT list of the batch dict
@@ -120,6 +125,7 @@ int ys_decode_infer(int n_levels, const float *const *level_x_host, const int *l
  *  per image: best class (first max), score > conf, xywh->xyxy, greedy NMS in score-descending
  *  order (ties: lower anchor index first), suppress when IoU > iou_thr; class_aware != 0 restricts
  *  suppression to same-class pairs (non-default).
+ *  Any A (above 16384 candidates per image the sort runs as segment sorts + merge).
  *  Outputs, each with row stride A per image, first keep_count[b] rows valid, score-descending:
  *   keep_anchor (B,A) i32 source anchor index, keep_boxes (B,A,4) = clamp(xyxy/img_size,0,1),
  *   keep_scores (B,A), keep_labels (B,A) i32, keep_count (B) i32.

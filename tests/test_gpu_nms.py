@@ -220,3 +220,27 @@ def test_nms_non_finite_and_inverted_boxes_vs_c_oracle(cuda_lib):
     boxes[78] = torch.tensor([float("nan"), 0.0, 5.0, 10.0])
     keep = nms_simple(boxes.cuda(), scores.cuda(), 0.5)
     assert keep == c_oracle.nms(boxes, scores, 0.5)
+
+
+@pytest.mark.parametrize("clustered", [False, True])
+def test_nms_1280px_candidate_count_vs_c_oracle(cuda_lib, clustered):
+    """33600 candidates per image (validation at 1280 px, the resolution of BASELINE configs[4]): more keys than one
+    shared-memory sort holds -- segment sorts + merge, then the shared-memory-free suppress path.  The reference's
+    nms_simple has no size limit (train_yolo11_cuda.py:361-399)."""
+    from oracle import c_oracle
+    from yolo_scratch_b200.train_yolo11_cuda import nms_batched, nms_simple
+    A = 33600
+    pred = synth.make_nms_predictions(2, A, 4, 1280, seed=330 + int(clustered), clustered=clustered, n_clusters=400)
+    ka, kb, ks, kl, kc = nms_batched(pred.cuda(), 0.001, 0.7, 1280)
+    for b in range(2):
+        xyxy, sc, cl, src = c_oracle.filter_candidates(pred[b], 0.001)
+        assert len(src) > 16384
+        keep = c_oracle.nms(xyxy, sc, 0.7)
+        k = int(kc[b])
+        assert k == len(keep)
+        assert np.array_equal(ka[b, :k].cpu().numpy(), src[keep])
+        assert np.array_equal(ks[b, :k].cpu().numpy(), sc[keep])
+        assert np.array_equal(kl[b, :k].cpu().numpy(), cl[keep])
+        if b == 0:      # the single-image entry point on the same candidates (N > 16384)
+            k1 = nms_simple(torch.from_numpy(xyxy).cuda(), torch.from_numpy(sc).cuda(), 0.7)
+            assert k1 == keep

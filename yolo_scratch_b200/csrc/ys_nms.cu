@@ -193,6 +193,63 @@ k_nms_sort(const unsigned long long *__restrict__ keys, const int *__restrict__ 
 }
 
 // ---------------------------------------------------------------------------------------------------
+// sort of more than kSortMaxN keys per image (1280 px validation: 33600 candidates; the reference's nms_simple has no
+// limit, train_yolo11_cuda.py:361-399).  The image's keys are cut into segments of kSortMaxN: k_nms_sort_seg sorts every
+// segment in shared memory (one block per segment, descending) and writes it back; k_nms_merge then gives every key its
+// final rank = its index inside its own segment + the number of larger keys in every other segment (one binary search
+// per other segment; keys are unique) and gathers the box / class / anchor into sorted order, as k_nms_sort does.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSortThreads)
+k_nms_sort_seg(const unsigned long long *__restrict__ keys, const int *__restrict__ count, int A,
+               unsigned long long *__restrict__ keys_sorted) {
+    extern __shared__ unsigned long long s_keys[];
+    const int b = blockIdx.y, seg = blockIdx.x;
+    const int n = count[b];
+    const int lo = seg * kSortMaxN;
+    if (lo >= n) return;
+    const int m = min(kSortMaxN, n - lo);
+    int P = 1;
+    while (P < m) P <<= 1;
+    const unsigned long long *src = keys + (size_t)b * A + lo;
+    for (int i = threadIdx.x; i < P; i += kSortThreads) s_keys[i] = i < m ? src[i] : 0ull;      // real keys are never 0
+    __syncthreads();
+    if (P > 1) nms_bitonic_desc(s_keys, P);
+    unsigned long long *dst = keys_sorted + (size_t)b * A + lo;
+    for (int i = threadIdx.x; i < m; i += kSortThreads) dst[i] = s_keys[i];
+}
+
+__global__ void __launch_bounds__(256)
+k_nms_merge(const unsigned long long *__restrict__ keys_sorted, const int *__restrict__ count, int A,
+            const float4 *__restrict__ boxes, const int *__restrict__ cls, float4 *__restrict__ sbox,
+            float *__restrict__ sscore, int *__restrict__ scls, int *__restrict__ sanchor) {
+    const int b = blockIdx.y;
+    const int n = count[b];
+    const int r = blockIdx.x * 256 + threadIdx.x;
+    if (r >= n) return;
+    const unsigned long long *base = keys_sorted + (size_t)b * A;
+    const unsigned long long key = base[r];
+    const int seg = r / kSortMaxN;
+    int pos = r - seg * kSortMaxN;
+    const int nseg = (n + kSortMaxN - 1) / kSortMaxN;
+    for (int s2 = 0; s2 < nseg; ++s2) {
+        if (s2 == seg) continue;
+        const unsigned long long *other = base + (size_t)s2 * kSortMaxN;
+        int lo = 0, hi = min(kSortMaxN, n - s2 * kSortMaxN);
+        while (lo < hi) {                         // number of keys of segment s2 larger than this one (it descends)
+            const int mid = (lo + hi) >> 1;
+            if (other[mid] > key) lo = mid + 1; else hi = mid;
+        }
+        pos += lo;
+    }
+    const int a = (int)(0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull));
+    const size_t o = (size_t)b * A + pos;
+    sbox[o] = boxes[(size_t)b * A + a];
+    sscore[o] = score_from_ordered((unsigned)(key >> 32));
+    scls[o] = cls ? cls[(size_t)b * A + a] : 0;
+    sanchor[o] = a;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // suppress
 // ---------------------------------------------------------------------------------------------------
 // IoU(i, j) > thr with the reference's arithmetic (train_yolo11_cuda.py:418-435, :396).
@@ -725,7 +782,7 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
 }
 
 struct NmsWorkspace {
-    unsigned long long *keys;
+    unsigned long long *keys, *keys2;      // keys2: segment-sorted keys, only when A > kSortMaxN
     float4 *boxes, *sbox;
     int *cls, *scls, *sanchor, *count;
     float *sscore;
@@ -736,6 +793,7 @@ static void carve_nms(NmsWorkspace &W, void *base, size_t cap, int B, int A) {
     const size_t n = (size_t)B * A;
     W.count = c.take<int>((size_t)B + 1);
     W.keys = c.take<unsigned long long>(n);
+    W.keys2 = A > kSortMaxN ? c.take<unsigned long long>(n) : nullptr;
     W.boxes = c.take<float4>(n);
     W.sbox = c.take<float4>(n);
     W.cls = c.take<int>(n);
@@ -753,9 +811,8 @@ static size_t suppress_smem_bytes(int A, int smem_boxes) {
 static int run_sort_suppress(const NmsWorkspace &W, int B, int A, float iou_thr, float img_size, int class_aware,
                              const float4 *boxes, const int *cls, int32_t *keep_anchor, float *keep_boxes,
                              float *keep_scores, int32_t *keep_labels, int32_t *keep_count, cudaStream_t stream) {
-    YS_REQUIRE(A <= kSortMaxN, YS_ERR_UNSUPPORTED, "NMS handles at most %d candidates per image (got %d)", kSortMaxN, A);
     int P = 1;
-    while (P < A) P <<= 1;
+    while (P < A && P < kSortMaxN) P <<= 1;
     const size_t sort_smem = (size_t)P * sizeof(unsigned long long);
     static DeviceOnce once_sort, once_sup[2];
     int rc = optin_smem((const void *)k_nms_sort, kSortMaxN * 8, once_sort, "k_nms_sort");
@@ -764,8 +821,20 @@ static int run_sort_suppress(const NmsWorkspace &W, int B, int A, float iou_thr,
     if (rc) return rc;
     rc = optin_smem((const void *)k_nms_suppress<true>, 220 * 1024, once_sup[1], "k_nms_suppress");
     if (rc) return rc;
-    k_nms_sort<<<B, kSortThreads, sort_smem, stream>>>(W.keys, W.count, A, boxes, cls, W.sbox, W.sscore, W.scls, W.sanchor);
-    YS_CHECK_LAUNCH("k_nms_sort");
+    if (A <= kSortMaxN) {
+        k_nms_sort<<<B, kSortThreads, sort_smem, stream>>>(W.keys, W.count, A, boxes, cls, W.sbox, W.sscore, W.scls, W.sanchor);
+        YS_CHECK_LAUNCH("k_nms_sort");
+    } else {
+        static DeviceOnce once_seg;
+        rc = optin_smem((const void *)k_nms_sort_seg, kSortMaxN * 8, once_seg, "k_nms_sort_seg");
+        if (rc) return rc;
+        YS_REQUIRE(B <= 65535, YS_ERR_UNSUPPORTED, "B must be <= 65535 (grid.y) when A > %d", kSortMaxN);
+        const int nseg = (A + kSortMaxN - 1) / kSortMaxN;
+        k_nms_sort_seg<<<dim3(nseg, B), kSortThreads, (size_t)kSortMaxN * 8, stream>>>(W.keys, W.count, A, W.keys2);
+        YS_CHECK_LAUNCH("k_nms_sort_seg");
+        k_nms_merge<<<dim3((A + 255) / 256, B), 256, 0, stream>>>(W.keys2, W.count, A, boxes, cls, W.sbox, W.sscore, W.scls, W.sanchor);
+        YS_CHECK_LAUNCH("k_nms_merge");
+    }
     if (A <= 9 * kRegThreads) {      // register-resident columns (every 640 px / 8400-candidate case)
 #define YS_LAUNCH_REG(CA, COLS)                                                                                              \
     k_nms_suppress_zreg<CA, COLS><<<B, kRegThreads, 0, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr,      \
