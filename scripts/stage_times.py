@@ -84,9 +84,7 @@ def main():
     call()
     res["loss_us"] = timed(4, args.reps)
     res["loss_fwd_only_us"] = timed(4, args.reps, fwd_only=True)
-    res["loss_legacy_fwd_only_us"] = timed(4 | 512, args.reps, fwd_only=True)
     call()
-    res["loss_legacy_us"] = timed(4 | 512, args.reps)
     res["full2_us"] = timed(0, args.reps)
     res["img_per_s"] = B / (res["full2_us"] * 1e-6)
     res["loss_items"] = out.tolist()

@@ -17,11 +17,12 @@ SOURCES = ["ys_api.cu", "ys_loss.cu", "ys_nms.cu", "ys_decode.cu", "ys_metrics.c
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
-    "--shared", "-Xcompiler", "-fPIC",
+    "-Xcompiler", "-fPIC",
     # host side of the bit-exact helpers must not contract a*b+c either
     "-Xcompiler", "-ffp-contract=off",
     "-Xptxas", "-v",
 ]
+OBJ_DIR = os.path.join(HERE, "build")
 
 
 def _nvcc() -> str:
@@ -31,27 +32,58 @@ def _nvcc() -> str:
     return "nvcc"
 
 
+def _deps():
+    return glob.glob(os.path.join(CSRC, "*")) + glob.glob(os.path.join(HERE, "..", "include", "*.h")) + [__file__]
+
+
 def needs_build() -> bool:
     if not os.path.exists(SO):
         return True
     t = os.path.getmtime(SO)
-    deps = glob.glob(os.path.join(CSRC, "*")) + glob.glob(os.path.join(HERE, "..", "include", "*.h")) + [__file__]
-    return any(os.path.getmtime(p) > t for p in deps)
+    return any(os.path.getmtime(p) > t for p in _deps())
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
+    """One nvcc -c per source (in parallel), then one link.  Objects are reused when neither their source nor any
+    header changed and the extra flags are the same."""
     if not force and not needs_build():
         return SO
+    from concurrent.futures import ThreadPoolExecutor
     extra = os.environ.get("YS_NVCC_EXTRA", "").split()      # tuning experiments only (scripts/gpu_tune.sh)
-    cmd = [_nvcc()] + NVCC_FLAGS + extra + ["-o", SO] + [os.path.join(CSRC, s) for s in SOURCES]
-    proc = subprocess.run(cmd, capture_output=True, text=True)
-    log = proc.stdout + proc.stderr
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    stamp = os.path.join(OBJ_DIR, "flags.txt")
+    flags_now = " ".join(NVCC_FLAGS + extra)
+    flags_same = os.path.exists(stamp) and open(stamp).read() == flags_now
+    headers = [p for p in _deps() if not p.endswith(".cu")]
+    newest_header = max(os.path.getmtime(p) for p in headers)
+
+    def compile_one(src):
+        obj = os.path.join(OBJ_DIR, src.replace(".cu", ".o"))
+        path = os.path.join(CSRC, src)
+        if (not force and flags_same and os.path.exists(obj) and os.path.getmtime(obj) > os.path.getmtime(path)
+                and os.path.getmtime(obj) > newest_header):
+            return obj, 0, f"[cached] {src}\n"
+        cmd = [_nvcc()] + NVCC_FLAGS + extra + ["-c", "-o", obj, path]
+        proc = subprocess.run(cmd, capture_output=True, text=True)
+        return obj, proc.returncode, " ".join(cmd) + "\n" + proc.stdout + proc.stderr
+
+    with ThreadPoolExecutor(max_workers=min(len(SOURCES), os.cpu_count() or 1)) as ex:
+        results = list(ex.map(compile_one, SOURCES))
+    log = "".join(r[2] for r in results)
+    rc = max(r[1] for r in results)
+    if rc == 0:
+        cmd = [_nvcc(), "--shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", SO] + [r[0] for r in results]
+        proc = subprocess.run(cmd, capture_output=True, text=True)
+        log += " ".join(cmd) + "\n" + proc.stdout + proc.stderr
+        rc = proc.returncode
     with open(os.path.join(HERE, "build.log"), "w") as f:
-        f.write(" ".join(cmd) + "\n" + log)
-    if verbose or proc.returncode != 0:
+        f.write(log)
+    if verbose or rc != 0:
         print(log)
-    if proc.returncode != 0:
-        raise RuntimeError(f"nvcc failed ({proc.returncode}); see {os.path.join(HERE, 'build.log')}")
+    if rc != 0:
+        raise RuntimeError(f"nvcc failed ({rc}); see {os.path.join(HERE, 'build.log')}")
+    with open(stamp, "w") as f:
+        f.write(flags_now)
     return SO
 
 
