@@ -665,6 +665,10 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
         P.items_per_img = L.n_hsegs + L.n_chunks * P.n_groups;
         YS_REQUIRE((long long)B * P.items_per_img < 2147483647LL / 2, YS_ERR_UNSUPPORTED, "too many work items");
         P.total_items = B * P.items_per_img;
+        P.ipi_magic = (unsigned)(0x100000000ull / (unsigned long long)P.items_per_img);
+        P.nch_magic = (unsigned)(0x100000000ull / (unsigned long long)(L.n_chunks > 0 ? L.n_chunks : 1));
+        if (P.items_per_img == 1) P.ipi_magic = 0xFFFFFFFFu;      // 2^32 does not fit: x * (2^32 - 1) >> 32 = x - 1, corrected once
+        if (L.n_chunks == 1) P.nch_magic = 0xFFFFFFFFu;
         P.hyp_box = hyp_box; P.hyp_cls = hyp_cls; P.hyp_dfl = hyp_dfl; P.batch = (float)B;
         const int want = (P.total_items + kStreamWarps - 1) / kStreamWarps;
         const unsigned blocks = (unsigned)(want < sms ? (want > 0 ? want : 1) : (sms > 4096 ? 4096 : sms));

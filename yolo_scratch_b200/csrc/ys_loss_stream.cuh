@@ -59,6 +59,7 @@ struct StreamParams {
     int total_items;         // B * items_per_img
     unsigned n_groups16;     // groups of kStreamWarps consecutive items (one item per warp of a CTA)
     unsigned rounds;         // ceil(n_groups16 / gridDim.x): every CTA runs this many rounds (groups past the end are padding)
+    unsigned ipi_magic, nch_magic;   // floor(2^32 / items_per_img), floor(2^32 / n_chunks): division by multiply-high
     unsigned rotate;         // per-round rotation of the CTA -> group map inside the round's window (see the kernel)
     float hyp_box, hyp_cls, hyp_dfl;
     float batch;
@@ -112,8 +113,11 @@ __device__ __forceinline__ Item decode_item(const LevelSet &L, const StreamParam
         it.b = 0; it.l = 0; it.hw = 0; it.i0 = 0; it.group = -1; it.n_live = 0;
         return it;
     }
-    it.b = item / P.items_per_img;
-    const int r = item - it.b * P.items_per_img;
+    // item / items_per_img by multiply-high with floor(2^32 / d) (never too large, at most one too small: one correction)
+    int bq = (int)__umulhi((unsigned)item, P.ipi_magic);
+    int r = item - bq * P.items_per_img;
+    if (r >= P.items_per_img) { ++bq; r -= P.items_per_img; }
+    it.b = bq;
     // Items of an image: first the box items, then the class items (see the schedule note in the kernel; interleaving
     // the two kinds in proportion measured 4 % slower).
     int l = 0;
@@ -132,8 +136,10 @@ __device__ __forceinline__ Item decode_item(const LevelSet &L, const StreamParam
         it.group = q - chunk * P.n_groups;
 #else
         // group-major: consecutive items (= the warps of one CTA) walk consecutive 512-byte pieces of the same rows
-        it.group = q / L.n_chunks;
-        const int chunk = q - it.group * L.n_chunks;
+        int gq = (int)__umulhi((unsigned)q, P.nch_magic);
+        int chunk = q - gq * L.n_chunks;
+        if (chunk >= L.n_chunks) { ++gq; chunk -= L.n_chunks; }
+        it.group = gq;
 #endif
 #pragma unroll
         for (int k = 1; k < YS_MAX_LEVELS; ++k)
