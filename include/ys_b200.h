@@ -108,6 +108,22 @@ int ys_assign(int B, int A, int G, int nc,
               uint8_t *fg_mask, int64_t *target_gt_idx, float *norm,
               void *workspace, size_t workspace_bytes, void *stream);
 
+/* The same entry point with the two non-default assignment modes north_star names (the reference runs
+ * neither: it stores topk and never reads it, losses/yolo_v8_loss.py:70-76, and uses plain IoU, :199):
+ *  topk > 0          per GT, only the topk anchors with the largest alignment metric among the anchors inside it (metric
+ *                    > 0) stay in the positive mask before the forced-assignment loops (k_topk_select: radix select on
+ *                    the metric bits + warp ballots).  Parity unpinned by the reference; oracle: oracle/ref_port.assign.
+ *  ciou_assign != 0  the pair metric is clamp(bbox_iou(CIoU=True), 0) (:46-56) instead of clamp(IoU, 0).
+ * topk = 0, ciou_assign = 0 is ys_assign. */
+size_t ys_assign_ex_workspace_bytes(int B, int A, int G, int topk);
+int ys_assign_ex(int B, int A, int G, int nc,
+                 const float *pd_scores, const float *pd_bboxes, const float *anc_points,
+                 const float *gt_labels, const float *gt_bboxes, const float *mask_gt,
+                 float alpha, float beta, float eps, int topk, int ciou_assign,
+                 float *target_labels, float *target_bboxes, float *target_scores,
+                 uint8_t *fg_mask, int64_t *target_gt_idx, float *norm,
+                 void *workspace, size_t workspace_bytes, void *stream);
+
 /* ---------------------------------------------------------------------------
  * Inference decode: DFL.forward + Detect.inference + dist2bbox(xywh=True, dim=1)
  * (models/yolo11_modules.py:180-192, :248-266, :303-312).

@@ -109,10 +109,19 @@ def _resolve(mp: torch.Tensor, ov: torch.Tensor):
 
 @torch.no_grad()
 def assign(pd_scores, pd_bboxes, anc_points, gt_labels, gt_bboxes, mask_gt,
-           num_classes: int = 80, alpha: float = 0.5, beta: float = 4.0, eps: float = EPS_ASSIGN):
+           num_classes: int = 80, alpha: float = 0.5, beta: float = 4.0, eps: float = EPS_ASSIGN,
+           ciou_assign: bool = False, topk: int = 0):
     """Returns (target_labels f32 (B,A), target_bboxes (B,A,4), target_scores (B,A,nc),
     fg_mask bool (B,A), target_gt_idx i64 (B,A)) exactly as the reference does,
-    including the odd G == 0 return (:100-108)."""
+    including the odd G == 0 return (:100-108).
+
+    Non-default modes (north_star wording; the reference itself runs neither):
+      ciou_assign  the pair metric is the reference's own bbox_iou(CIoU=True) (:46-56) clamped at 0 instead of plain IoU
+                   (:199) -- pinned by tests/golden/assign_ciou_s98.npz, a composition of reference code;
+      topk > 0     the positive mask keeps, per GT, only the `topk` anchors with the largest alignment metric among the
+                   anchors inside it (metric > 0) -- what `topk` would mean if the reference read it (:70-76, :363).
+                   PARITY UNPINNED BY THE REFERENCE: the semantics are this repository's (torch.topk over the anchor
+                   dimension of align_metric * mask_pos); the fixture assign_topk_s99.npz only freezes them."""
     B, A = pd_scores.shape[:2]
     G = gt_bboxes.shape[1]
     if G == 0:
@@ -121,7 +130,7 @@ def assign(pd_scores, pd_bboxes, anc_points, gt_labels, gt_bboxes, mask_gt,
                 torch.zeros_like(pd_scores), z, z.clone())
 
     # step 1: pair metrics (:196-208)
-    ov = pair_iou_xyxy(pd_bboxes.unsqueeze(2), gt_bboxes.unsqueeze(1)).squeeze(-1).clamp_(0)
+    ov = pair_iou_xyxy(pd_bboxes.unsqueeze(2), gt_bboxes.unsqueeze(1), ciou=ciou_assign).squeeze(-1).clamp_(0)
     cls_at_gt = pd_scores.gather(-1, gt_labels.long().unsqueeze(1).expand(-1, A, -1))
     am = cls_at_gt.pow(alpha) * ov.pow(beta)
     # step 2: anchor centre strictly inside the GT (:210-224), times GT validity (:192)
@@ -130,6 +139,10 @@ def assign(pd_scores, pd_bboxes, anc_points, gt_labels, gt_bboxes, mask_gt,
     gx1, gy1, gx2, gy2 = (gt_bboxes[..., i].unsqueeze(1) for i in range(4))
     inside = torch.stack((ax - gx1, ay - gy1, gx2 - ax, gy2 - ay), -1).amin(-1).gt(eps).float()
     mp = inside * mask_gt.unsqueeze(1)
+    if topk > 0:
+        metric = am * mp
+        vals, idx = torch.topk(metric, min(topk, A), dim=1)
+        mp = mp * torch.zeros_like(metric).scatter_(1, idx, (vals > 0).to(metric.dtype))
 
     # step 3: valid GT columns that own no anchor get their best-IoU anchor (:117-139;
     # the "inside" branch at :130-133 is dead: it re-tests the condition found false at :121)

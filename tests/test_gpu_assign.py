@@ -104,3 +104,37 @@ def test_every_valid_gt_owns_an_anchor_or_was_stolen(cuda_lib):
     frac = (owned * mask_gt).sum() / mask_gt.sum()
     assert frac > 0.9
     assert (ts.sum(-1)[~fg] == 0).all()
+
+
+@pytest.mark.parametrize("name", golden_names("assign_ciou") + golden_names("assign_topk"))
+def test_assigner_modes_golden(cuda_lib, name):
+    """use_topk / ciou_assign (keyword-only, default off) against fixtures built from compositions of reference code."""
+    from yolo_scratch_b200.losses import TaskAlignedAssigner
+    g = load_golden(name)
+    inp = [t(g[k]) for k in ("pd_scores", "pd_bboxes", "anc_points", "gt_labels", "gt_bboxes", "mask_gt")]
+    topk = int(g["topk"])
+    a = TaskAlignedAssigner(topk=topk or 50, num_classes=int(g["nc"]), alpha=0.5, beta=4.0, use_topk=topk > 0,
+                            ciou_assign=bool(int(g["ciou"])))
+    out = [o.cpu() for o in a.forward(*[x.cuda() for x in inp])]
+    ref = [t(g[k]) for k in ("target_labels", "target_bboxes", "target_scores", "fg_mask", "target_gt_idx")]
+    _check(out, ref)
+
+
+@pytest.mark.parametrize("seed,topk,ciou,B,max_gt,kw", [
+    (120, 10, False, 4, 20, {}),
+    (121, 13, False, 4, 20, {"p_tiny": 0.2, "p_nested": 0.3}),
+    (122, 1, False, 3, 40, {"p_nested": 0.3}),
+    (123, 0, True, 4, 20, {"p_tiny": 0.2, "p_nested": 0.3}),
+    (124, 5, True, 2, 30, {"p_nested": 0.4}),
+    (125, 9000, False, 2, 10, {}),            # k larger than the anchor count: every positive candidate stays
+])
+def test_assigner_modes_640_vs_port(cuda_lib, seed, topk, ciou, B, max_gt, kw):
+    """The modes at the 640 px shape (A = 8400) against the torch oracle (oracle/ref_port.assign): indices bit-exact
+    (continuous random inputs: alignment metrics are unique)."""
+    from oracle import ref_port as orc
+    from yolo_scratch_b200.losses import TaskAlignedAssigner
+    inp = synth.make_assigner_inputs(B, ((80, 80), (40, 40), (20, 20)), synth.LEVEL_STRIDES, 80, max_gt, seed, **kw)
+    a = TaskAlignedAssigner(topk=topk or 50, num_classes=80, alpha=0.5, beta=4.0, use_topk=topk > 0, ciou_assign=ciou)
+    out = [o.cpu() for o in a.forward(*[x.cuda() for x in inp])]
+    ref = orc.assign(*inp, 80, 0.5, 4.0, ciou_assign=ciou, topk=topk)
+    _check(out, ref)

@@ -100,3 +100,23 @@ def test_loss_unaligned_levels_port(name):
     assert torch.allclose(items, t(g["items"]), rtol=1e-6)
     assert torch.allclose(total.detach(), t(g["total"]), rtol=1e-6)
     check_imgsz_grads([l.grad for l in leaves], g, 1e-6)
+
+
+MODE_FIXTURES = golden_names("assign_ciou") + golden_names("assign_topk")
+
+
+@pytest.mark.parametrize("name", MODE_FIXTURES)
+def test_assigner_modes_port(name):
+    """Non-default assigner modes (north_star wording) of the port against compositions of reference code
+    (make_golden_r2.py: the reference assigner with its own bbox_iou(CIoU=True) as the pair metric; the reference forward
+    with mask_pos restricted to the per-GT top-k of align_metric).  top-k: parity unpinned by the reference itself."""
+    g = load_golden(name)
+    inp = [t(g[k]) for k in ("pd_scores", "pd_bboxes", "anc_points", "gt_labels", "gt_bboxes", "mask_gt")]
+    tl, tb, ts, fg, tgi = orc.assign(*inp, int(g["nc"]), 0.5, 4.0, ciou_assign=bool(int(g["ciou"])), topk=int(g["topk"]))
+    assert torch.equal(fg, t(g["fg_mask"]))
+    assert torch.equal(tgi.int(), t(g["target_gt_idx"]))
+    assert torch.equal(tl, t(g["target_labels"]))
+    assert torch.equal(tb, t(g["target_bboxes"]))
+    assert torch.allclose(ts, t(g["target_scores"]), rtol=1e-6, atol=1e-9)
+    base = orc.assign(*inp, int(g["nc"]), 0.5, 4.0)
+    assert not torch.equal(base[4], tgi), "the fixture must exercise the mode"

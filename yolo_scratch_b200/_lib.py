@@ -36,6 +36,9 @@ PROTOTYPES = {
     "ys_assign_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "ys_assign": (c_int, [c_int, c_int, c_int, c_int] + [c_void_p] * 6 + [c_float] * 3 + [c_void_p] * 6 +
                   [c_void_p, c_size_t, c_void_p]),
+    "ys_assign_ex_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "ys_assign_ex": (c_int, [c_int, c_int, c_int, c_int] + [c_void_p] * 6 + [c_float] * 3 + [c_int, c_int] + [c_void_p] * 6 +
+                     [c_void_p, c_size_t, c_void_p]),
     "ys_decode_infer": (c_int, [c_int, C.POINTER(c_void_p), C.POINTER(c_int), C.POINTER(c_int), C.POINTER(c_float),
                                 c_int, c_int, c_int, c_void_p, c_int, c_void_p]),
     "ys_nms_workspace_bytes": (c_size_t, [c_int, c_int]),

@@ -67,6 +67,10 @@ struct AssignIO {
     const int *img_order;       // fused only (else nullptr): blockIdx.y -> image, a scheduling hint from k_pack_gt
     int n_identity;             // fused only: the first n_identity launch slots are the images 0..n_identity-1 (see k_assign)
     int skip_fixup;             // profiling only
+    // dense entry point only, non-default modes (north_star wording; the reference runs neither)
+    int ciou;                   // 1: pair metric = clamp(CIoU, 0) (reference bbox_iou(CIoU=True)) instead of plain IoU
+    const unsigned *sel;        // top-k mode: bit a of row (b*G + g): anchor a is among GT g's top-k candidates; nullptr = off
+    int sel_words;              // words per row = ceil(A / 32)
     unsigned long long *best_key;   // per-GT arg-max key over all anchors: written by the scan for risk GT (zero on
                                     // entry), by the fix-up for the others when an image has more than kFixSmemGt GT
     int *forced;                // same: 8 ints per GT (forced x2, needy, kk, tg0, lost, spare x2)
@@ -143,6 +147,26 @@ __device__ __forceinline__ float iou_assign_lazy(float4 p, float area_p, float4 
     return iou < 0.f ? 0.f : iou;
 }
 
+// The assigner's pair metric.  Fused path: always the reference's plain IoU (:199).  Dense entry point: clamp(CIoU, 0) in
+// ciou mode -- CIoU <= IoU, so it clamps to 0 wherever the boxes do not intersect, exactly like the lazy IoU.
+template <bool FUSED, bool LAZY = true>
+__device__ __forceinline__ float pair_ov(const AssignIO &io, float4 p, float area_p, float4 q, float area_q) {
+    if (!FUSED && io.ciou) {
+        const float iw = YS_SUB(fminf2(p.z, q.z), fmaxf2(p.x, q.x));
+        const float ih = YS_SUB(fminf2(p.w, q.w), fmaxf2(p.y, q.y));
+        if (!(iw > 0.f) || !(ih > 0.f)) return 0.f;
+        const float c = ciou_pair(p, q);
+        return c < 0.f ? 0.f : c;
+    }
+    return LAZY ? iou_assign_lazy(p, area_p, q, area_q) : iou_assign(p, area_p, q, area_q);
+}
+// Top-k mode (dense entry point): is anchor a among the selected candidates of GT slot j of image b?
+template <bool FUSED>
+__device__ __forceinline__ bool sel_ok(const AssignIO &io, int gidx, int a) {
+    if (FUSED || io.sel == nullptr) return true;
+    return (io.sel[(size_t)gidx * io.sel_words + (a >> 5)] >> (a & 31)) & 1u;
+}
+
 // This anchor's centre (px) and, for the fused path, its grid position.
 template <bool FUSED>
 __device__ __forceinline__ void anchor_centre(const AssignIO &io, const LevelSet &L, int a, float &ax, float &ay) {
@@ -174,9 +198,9 @@ __device__ __forceinline__ int resolve_row(const AssignIO &io, const LevelSet &L
     unsigned long long best = 0ull;   // argmax over ALL slots of ov, first max
     for (int j = lane; j < n; j += 32) {
         float4 q = io.gt_box[g0 + j];
-        float ov = iou_assign(p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
+        float ov = pair_ov<FUSED, false>(io, p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
         bool valid = FUSED ? true : (io.gt_valid[g0 + j] != 0.f);
-        bool m = (centre_in_box(ax, ay, q) && valid) || forced[2 * j] == k || (with_loop2 && forced[2 * j + 1] == k);
+        bool m = (centre_in_box(ax, ay, q) && valid && sel_ok<FUSED>(io, g0 + j, k)) || forced[2 * j] == k || (with_loop2 && forced[2 * j + 1] == k);
         if (m) { ++cnt; first = min(first, (unsigned)j); }
         unsigned long long key = argmax_key(ov, (unsigned)j);
         if (ov >= 0.f && key > best) best = key;
@@ -191,7 +215,7 @@ __device__ __forceinline__ int resolve_row(const AssignIO &io, const LevelSet &L
     float ov = 0.f;
     if (g >= 0) {
         float4 q = io.gt_box[g0 + g];
-        ov = iou_assign(p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
+        ov = pair_ov<FUSED, false>(io, p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
     }
     ov_out = ov;
     return g;
@@ -232,8 +256,8 @@ __device__ __forceinline__ int resolve_row_group(const AssignIO &io, const Level
             for (int u = 0; u < 4; ++u) {
                 const int j = j0 + u * W;
                 if (j < n) {
-                    const float ov = iou_assign_lazy(p, area_p, q[u], area_eps_h(q[u].x, q[u].y, q[u].z, q[u].w));
-                    const bool m = (centre_in_box(ax, ay, q[u]) && valid[u]) || f[u].x == k || f[u].y == k;
+                    const float ov = pair_ov<FUSED>(io, p, area_p, q[u], area_eps_h(q[u].x, q[u].y, q[u].z, q[u].w));
+                    const bool m = (centre_in_box(ax, ay, q[u]) && valid[u] && sel_ok<FUSED>(io, g0 + j, k)) || f[u].x == k || f[u].y == k;
                     if (m) { ++cnt; first = min(first, (unsigned)j); }
                     if (ov > best_ov) { best_ov = ov; best_j = j; }
                 }
@@ -253,7 +277,7 @@ __device__ __forceinline__ int resolve_row_group(const AssignIO &io, const Level
     float ov = 0.f;
     if (active && g >= 0) {
         const float4 q = io.gt_box[g0 + g];
-        ov = iou_assign(p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
+        ov = pair_ov<FUSED, false>(io, p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
     }
     ov_out = ov;
     return g;
@@ -499,7 +523,7 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
             while (m) {
                 const int j = j0 + __ffs(m) - 1;
                 m &= m - 1;
-                if (live && centre_in_box(ax, ay, S.box[j])) {
+                if (live && centre_in_box(ax, ay, S.box[j]) && sel_ok<FUSED>(io, g0 + t0 + j, a)) {
                     if (first < 0) first = t0 + j;
                     ++cnt;
                     S.any[j] = 1;
@@ -582,7 +606,7 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
                     }
                 } else if (cnt > 1) {
                     for (int j = 0; j < tn; ++j) {
-                        const float ov = iou_assign_lazy(p, area_p, S.box[j], S.area[j]);
+                        const float ov = pair_ov<FUSED>(io, p, area_p, S.box[j], S.area[j]);
                         if (ov > best_ov) { best_ov = ov; best_g = t0 + j; }     // first maximum over ALL slots (:233)
                     }
                 }
@@ -604,7 +628,7 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     else if (cnt == 1) {
         g = first;
         const float4 q = one_tile ? S.box[first] : io.gt_box[g0 + first];
-        ov = iou_assign(p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
+        ov = pair_ov<FUSED, false>(io, p, area_p, q, area_eps_h(q.x, q.y, q.z, q.w));
     }
     float nrm = 0.f;
     int lb = -1;
@@ -694,7 +718,7 @@ __device__ __forceinline__ void fix_argmax(const LevelSet &L, const AssignIO &io
 #pragma unroll 8
         for (int a = tid; a < L.A; a += kScanThreads) {
             const float4 p = FUSED ? __ldcg(pb + a) : pb[a];
-            const float ov = iou_assign_lazy(p, area_eps_h(p.x, p.y, p.z, p.w), gq, area_q);
+            const float ov = pair_ov<FUSED>(io, p, area_eps_h(p.x, p.y, p.z, p.w), gq, area_q);
             if (ov > best) { best = ov; best_a = a; }
         }
         unsigned long long key = best >= 0.f ? argmax_key(best, (unsigned)best_a) : 0ull;

@@ -384,6 +384,96 @@ __global__ void k_assign_emit(int B, int A, int G, int nc, const int *__restrict
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Top-k mode of the dense assigner (non-default; north_star "alignment-metric top-k", SURVEY D1 -- the reference stores
+// `topk` and never reads it, losses/yolo_v8_loss.py:70-76): per GT, keep only the k anchors with the largest alignment
+// metric score[label]^alpha * overlap^beta among the anchors whose centre lies inside it (metric > 0).
+// One block per (GT, image).  The k-th largest metric is found by a 4-pass radix select on the metric's bit pattern
+// (positive floats order as unsigned integers; 256-bin histogram per pass, the metric is recomputed instead of stored),
+// then one ordered pass writes the selection bitmask row (one ballot word per warp).  Ties at the k-th value go to the
+// lower anchor index (torch.topk leaves them unspecified).
+// ---------------------------------------------------------------------------------------------------
+constexpr int kTopkThreads = 256;
+__global__ void __launch_bounds__(kTopkThreads)
+k_topk_select(int A, int G, int nc, const float *__restrict__ pd_scores, const float4 *__restrict__ pd_box,
+              const float2 *__restrict__ anc, const float *__restrict__ gt_labels, const float4 *__restrict__ gt_box,
+              const float *__restrict__ mask_gt, float alpha, float beta, int ciou, int topk, unsigned *__restrict__ sel,
+              int sel_words) {
+    __shared__ int s_hist[256];
+    __shared__ unsigned s_prefix;
+    __shared__ int s_need, s_eq, s_all;
+    const int g = blockIdx.x, b = blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned *out = sel + ((size_t)b * G + g) * sel_words;
+    if (mask_gt[(size_t)b * G + g] == 0.f) {
+        for (int w = tid; w < sel_words; w += kTopkThreads) out[w] = 0u;
+        return;
+    }
+    const float4 q = gt_box[(size_t)b * G + g];
+    const float area_q = area_eps_h(q.x, q.y, q.z, q.w);
+    int lab = (int)gt_labels[(size_t)b * G + g];
+    lab = lab < 0 ? 0 : (lab > nc - 1 ? nc - 1 : lab);
+    AssignIO io_m;                     // only the metric switch of pair_ov is read
+    io_m.ciou = ciou;
+    auto metric_bits = [&](int a) -> unsigned {
+        if (a >= A) return 0u;
+        const float2 c = anc[a];
+        if (!centre_in_box(c.x, c.y, q)) return 0u;
+        const float4 p = pd_box[(size_t)b * A + a];
+        const float ov = pair_ov<false, false>(io_m, p, area_eps_h(p.x, p.y, p.z, p.w), q, area_q);
+        const float sc = pd_scores[((size_t)b * A + a) * nc + lab];
+        const float m = pow_special(sc, alpha) * pow_special(ov, beta);      // align_metric (:206)
+        return m > 0.f ? __float_as_uint(m) : 0u;
+    };
+    if (tid == 0) { s_prefix = 0u; s_need = topk; s_all = 0; s_eq = 0; }
+    for (int pass = 0; pass < 4; ++pass) {
+        for (int i = tid; i < 256; i += kTopkThreads) s_hist[i] = 0;
+        __syncthreads();
+        if (s_all) break;                                   // fewer positive candidates than k: everything is selected
+        const int shift = 24 - 8 * pass;
+        const unsigned prefix = s_prefix;
+        for (int a = tid; a < A; a += kTopkThreads) {
+            const unsigned bits = metric_bits(a);
+            if (bits != 0u && (pass == 0 || (bits >> (shift + 8)) == prefix)) atomicAdd(&s_hist[(bits >> shift) & 255u], 1);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int need = s_need, bin = 255, cum = 0;
+            for (; bin >= 0; --bin) {
+                if (cum + s_hist[bin] >= need) break;
+                cum += s_hist[bin];
+            }
+            if (bin < 0) {
+                s_all = 1;                                  // only possible in pass 0
+            } else {
+                s_need = need - cum;
+                s_eq = s_hist[bin];
+                s_prefix = (prefix << 8) | (unsigned)bin;
+            }
+        }
+        __syncthreads();
+    }
+    const bool all = s_all != 0;
+    const unsigned T = all ? 1u : s_prefix;                 // the k-th largest metric (bit pattern)
+    const bool take_eq = all || s_eq <= s_need;             // every candidate equal to T fits
+    for (int base = 0; base < sel_words * 32; base += kTopkThreads) {
+        const int a = base + tid;
+        const unsigned bits = metric_bits(a);
+        const bool on = bits != 0u && (bits > T || (bits == T && take_eq));
+        const unsigned m = __ballot_sync(0xffffffffu, on);
+        const int w = (base >> 5) + warp;
+        if (lane == 0 && w < sel_words) out[w] = m;
+    }
+    if (!take_eq) {                                          // ties at the k-th value: the lowest anchors first
+        __syncthreads();
+        if (tid == 0) {
+            int need = s_need;
+            for (int a = 0; a < A && need > 0; ++a)
+                if (metric_bits(a) == T) { out[a >> 5] |= 1u << (a & 31); --need; }
+        }
+    }
+}
+
 static int build_levels(LevelSet &L, int n_levels, const float *const *xs, float *const *gs, const int *hs,
                         const int *ws, const float *strides, int nc, int reg_max) {
     YS_REQUIRE(n_levels >= 1 && n_levels <= YS_MAX_LEVELS, YS_ERR_BAD_ARG, "n_levels must be in [1,%d]", YS_MAX_LEVELS);
@@ -624,6 +714,7 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
     // stream, the producer of the head outputs included, has completed before it starts)
     io.n_identity = (stages & YS_STAGE_PACK) ? (io.img_order ? n_identity : B) : 0;
     io.skip_fixup = (stages & YS_STAGE_DIAG_NOFIXUP) ? 1 : 0;
+    io.ciou = 0; io.sel = nullptr; io.sel_words = 0;
     // optional exports: written in place when the padded anchor space is the reference's (every h*w % 4 == 0), else
     // kept in the workspace and remapped by k_export_state after the assignment
     const bool remap = L.A != L.A_true;
@@ -735,11 +826,12 @@ struct AssignWorkspace {
     unsigned long long *best_key;
     float *norm, *tss, *scan_partial;
     double *img_sum;
+    unsigned *sel;       // top-k mode: selection bitmask (B*G rows of ceil(A/32) words)
     unsigned *counters;  // [0] images finished, [2 + b] blocks of image b finished
     size_t zero_bytes;   // leading region that must be zeroed per call
     size_t bytes;
 };
-static void carve_assign(AssignWorkspace &W, void *base, size_t cap, int B, int A, int G) {
+static void carve_assign(AssignWorkspace &W, void *base, size_t cap, int B, int A, int G, int topk = 0) {
     Carver c(base, cap);
     const size_t N = (size_t)B * G;
     W.counters = c.take<unsigned>((size_t)B + 2);
@@ -753,6 +845,7 @@ static void carve_assign(AssignWorkspace &W, void *base, size_t cap, int B, int 
     W.scan_partial = c.take<float>((size_t)B * scan_blocks(A));
     W.tgi = c.take<int>((size_t)B * A);
     W.norm = c.take<float>((size_t)B * A);
+    W.sel = topk > 0 ? c.take<unsigned>(N * (size_t)((A + 31) / 32)) : nullptr;
     W.bytes = align_up(c.off, 256);
 }
 }  // namespace ys
@@ -762,13 +855,31 @@ extern "C" size_t ys_assign_workspace_bytes(int B, int A, int G) {
     carve_assign(W, nullptr, 0, B > 0 ? B : 1, A > 0 ? A : 1, G > 0 ? G : 1);
     return W.bytes;
 }
+extern "C" size_t ys_assign_ex_workspace_bytes(int B, int A, int G, int topk) {
+    AssignWorkspace W;
+    carve_assign(W, nullptr, 0, B > 0 ? B : 1, A > 0 ? A : 1, G > 0 ? G : 1, topk);
+    return W.bytes;
+}
 
 extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, const float *pd_bboxes,
                          const float *anc_points, const float *gt_labels, const float *gt_bboxes,
                          const float *mask_gt, float alpha, float beta, float eps, float *target_labels,
                          float *target_bboxes, float *target_scores, uint8_t *fg_mask, int64_t *target_gt_idx,
                          float *norm_out, void *workspace, size_t workspace_bytes, void *stream_v) {
+    return ys_assign_ex(B, A, G, nc, pd_scores, pd_bboxes, anc_points, gt_labels, gt_bboxes, mask_gt, alpha, beta, eps, 0, 0,
+                        target_labels, target_bboxes, target_scores, fg_mask, target_gt_idx, norm_out, workspace,
+                        workspace_bytes, stream_v);
+}
+
+extern "C" int ys_assign_ex(int B, int A, int G, int nc, const float *pd_scores, const float *pd_bboxes,
+                            const float *anc_points, const float *gt_labels, const float *gt_bboxes,
+                            const float *mask_gt, float alpha, float beta, float eps, int topk, int ciou_assign,
+                            float *target_labels, float *target_bboxes, float *target_scores, uint8_t *fg_mask,
+                            int64_t *target_gt_idx, float *norm_out, void *workspace, size_t workspace_bytes,
+                            void *stream_v) {
     cudaStream_t stream = (cudaStream_t)stream_v;
+    YS_REQUIRE(topk >= 0, YS_ERR_BAD_ARG, "topk must be >= 0 (0 = off, the reference's behaviour)");
+    YS_REQUIRE(topk == 0 || G <= 65535, YS_ERR_UNSUPPORTED, "top-k mode: G must be <= 65535 (grid.x)");
     YS_REQUIRE(B >= 1 && A >= 1 && G >= 1 && nc >= 1, YS_ERR_BAD_ARG, "B, A, G, nc must be >= 1");
     YS_REQUIRE(B <= 65535, YS_ERR_UNSUPPORTED, "B must be <= 65535 (grid.y)");
     YS_REQUIRE(pd_scores && pd_bboxes && anc_points && gt_labels && gt_bboxes && mask_gt, YS_ERR_BAD_ARG, "null input");
@@ -776,7 +887,7 @@ extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, co
     YS_REQUIRE((((uintptr_t)pd_bboxes | (uintptr_t)gt_bboxes | (uintptr_t)target_bboxes) & 15) == 0 &&
                    ((uintptr_t)anc_points & 7) == 0, YS_ERR_BAD_ARG, "box pointers must be 16-byte aligned, anc_points 8-byte");
     AssignWorkspace W;
-    carve_assign(W, workspace, workspace_bytes, B, A, G);
+    carve_assign(W, workspace, workspace_bytes, B, A, G, topk);
     YS_REQUIRE(W.bytes <= workspace_bytes, YS_ERR_WORKSPACE, "workspace too small: need %zu, got %zu", W.bytes, workspace_bytes);
     YS_REQUIRE(((uintptr_t)workspace & 255) == 0, YS_ERR_BAD_ARG, "workspace must be 256-byte aligned");
     cudaMemsetAsync(workspace, 0, W.zero_bytes, stream);
@@ -792,6 +903,15 @@ extern "C" int ys_assign(int B, int A, int G, int nc, const float *pd_scores, co
     io.gt_label_f = gt_labels; io.gt_valid = mask_gt; io.pd_box = (const float4 *)pd_bboxes; io.pd_scores = pd_scores;
     io.anc = (const float2 *)anc_points; io.best_key = W.best_key; io.owned_cnt = W.owned_cnt; io.gt_flags = W.gt_flags;
     io.img_order = nullptr; io.n_identity = 0; io.skip_fixup = 0;
+    io.ciou = ciou_assign ? 1 : 0; io.sel = nullptr; io.sel_words = (A + 31) / 32;
+    if (topk > 0) {
+        k_topk_select<<<dim3(G, B), kTopkThreads, 0, stream>>>(A, G, nc, pd_scores, (const float4 *)pd_bboxes,
+                                                               (const float2 *)anc_points, gt_labels,
+                                                               (const float4 *)gt_bboxes, mask_gt, alpha, beta, io.ciou, topk,
+                                                               W.sel, io.sel_words);
+        YS_CHECK_LAUNCH("k_topk_select");
+        io.sel = W.sel;
+    }
     io.forced = W.forced; io.pbox = nullptr; io.tgi = W.tgi; io.lab = nullptr; io.norm = norm_out ? norm_out : W.norm;
     io.partial = W.scan_partial; io.img_sum = W.img_sum; io.tss = W.tss;
     io.done_counter = W.counters; io.img_done = W.counters + 2;

@@ -57,6 +57,26 @@ YS_HD float iou_assign(float4 p, float area_p, float4 q, float area_q) {
     return iou < 0.f ? 0.f : iou;
 }
 
+// bbox_iou(xywh=False, CIoU=True) in the reference's operation order (losses/yolo_v8_loss.py:31-56), unclamped: the
+// pair metric of the non-default ciou_assign mode of the assigner.  atanf is the only non-exact step.
+YS_HD float ciou_pair(float4 p, float4 q) {
+    const float eps = kEpsIou;
+    const float w1 = YS_SUB(p.z, p.x), h1 = YS_ADD(YS_SUB(p.w, p.y), eps);
+    const float w2 = YS_SUB(q.z, q.x), h2 = YS_ADD(YS_SUB(q.w, q.y), eps);
+    const float inter = inter_area(p.x, p.y, p.z, p.w, q.x, q.y, q.z, q.w);
+    const float uni = YS_ADD(YS_SUB(YS_ADD(YS_MUL(w1, h1), YS_MUL(w2, h2)), inter), eps);
+    const float iou = YS_DIV(inter, uni);
+    const float cw = YS_SUB(fmaxf2(p.z, q.z), fminf2(p.x, q.x));
+    const float ch = YS_SUB(fmaxf2(p.w, q.w), fminf2(p.y, q.y));
+    const float c2 = YS_ADD(YS_ADD(YS_MUL(cw, cw), YS_MUL(ch, ch)), eps);
+    const float sx = YS_SUB(YS_SUB(YS_ADD(q.x, q.z), p.x), p.z), sy = YS_SUB(YS_SUB(YS_ADD(q.y, q.w), p.y), p.w);
+    const float rho2 = YS_DIV(YS_ADD(YS_MUL(sx, sx), YS_MUL(sy, sy)), 4.f);
+    const float dat = YS_SUB(atanf(YS_DIV(w2, h2)), atanf(YS_DIV(w1, h1)));
+    const float v = YS_MUL(0.40528473456935108578f, YS_MUL(dat, dat));
+    const float alpha = YS_DIV(v, YS_ADD(YS_SUB(v, iou), YS_ADD(1.f, eps)));
+    return YS_SUB(iou, YS_ADD(YS_DIV(rho2, c2), YS_MUL(v, alpha)));
+}
+
 // Anchor centre strictly inside the GT (losses/yolo_v8_loss.py:220-224)
 YS_HD bool centre_in_box(float ax, float ay, float4 q) {
     float d = fminf2(fminf2(YS_SUB(ax, q.x), YS_SUB(ay, q.y)), fminf2(YS_SUB(q.z, ax), YS_SUB(q.w, ay)));

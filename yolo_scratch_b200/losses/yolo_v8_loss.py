@@ -106,15 +106,22 @@ def bbox_iou(box1, box2, xywh=True, GIoU=False, DIoU=False, CIoU=False, eps=1e-7
 # ----------------------------------------------------------------------------------------------
 class TaskAlignedAssigner(nn.Module):
     """Same constructor and forward contract as the reference class (losses/yolo_v8_loss.py:64-180).
-    `topk` is accepted and, as in the reference, never used."""
+    `topk` is accepted and, as in the reference, never used -- unless one of the two keyword-only,
+    default-off modes north_star names is switched on:
+      use_topk=True     per GT, only the `topk` anchors with the largest alignment metric among the anchors inside it
+                        stay positive before the forced-assignment loops (what `topk` would mean if the reference read
+                        it; semantics defined by oracle/ref_port.assign(topk=...), parity unpinned by the reference);
+      ciou_assign=True  the pair metric is the reference's own bbox_iou(CIoU=True) clamped at 0 instead of plain IoU."""
 
-    def __init__(self, topk=13, num_classes=80, alpha=1.0, beta=6.0, eps=1e-9):
+    def __init__(self, topk=13, num_classes=80, alpha=1.0, beta=6.0, eps=1e-9, *, use_topk=False, ciou_assign=False):
         super().__init__()
         self.topk = topk
         self.num_classes = num_classes
         self.alpha = alpha
         self.beta = beta
         self.eps = eps
+        self.use_topk = bool(use_topk)
+        self.ciou_assign = bool(ciou_assign)
         self._ws = _lib.Workspace()
 
     @torch.no_grad()
@@ -137,11 +144,13 @@ class TaskAlignedAssigner(nn.Module):
         ts = torch.empty(B, A, self.num_classes, device=dev)
         fg = torch.empty(B, A, device=dev, dtype=torch.uint8)
         tgi = torch.empty(B, A, device=dev, dtype=torch.int64)
-        ws = self._ws.get(lib.ys_assign_workspace_bytes(B, A, G), dev)
+        topk = int(self.topk) if self.use_topk else 0
+        ws = self._ws.get(lib.ys_assign_ex_workspace_bytes(B, A, G, topk), dev)
         with _lib.on_device(ps):
-            check(lib.ys_assign(B, A, G, self.num_classes, ptr(ps), ptr(pb), ptr(an), ptr(gl), ptr(gb), ptr(mg),
-                                float(self.alpha), float(self.beta), float(self.eps), ptr(tl), ptr(tb), ptr(ts), ptr(fg),
-                                ptr(tgi), 0, ptr(ws), ws.numel(), stream_ptr(dev)), "ys_assign")
+            check(lib.ys_assign_ex(B, A, G, self.num_classes, ptr(ps), ptr(pb), ptr(an), ptr(gl), ptr(gb), ptr(mg),
+                                   float(self.alpha), float(self.beta), float(self.eps), topk, int(self.ciou_assign),
+                                   ptr(tl), ptr(tb), ptr(ts), ptr(fg), ptr(tgi), 0, ptr(ws), ws.numel(), stream_ptr(dev)),
+                  "ys_assign_ex")
         return tl, tb, ts, fg.bool(), tgi
 
 
