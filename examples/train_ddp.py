@@ -33,6 +33,57 @@ from yolo_scratch_b200 import synth  # noqa: E402
 from yolo_scratch_b200.losses import v8DetectionLoss  # noqa: E402
 
 
+def check_grads(args, net, model, criterion, img, batch, rank, world, dev):
+    """The multi-GPU oracle of SURVEY §8e: the path is per-image independent and each rank normalises its own loss, so DDP's
+    gradient mean must equal the mean over ranks of the per-shard reference gradients.  Per rank: (1) the product step --
+    forward through DDP, CUDA criterion, backward: parameter gradients averaged by NCCL; (2) the oracle -- the same head
+    tensors through oracle/ref_port.detection_loss on the CPU, its head gradients back-propagated through the SAME
+    autograd graph of the unwrapped module (no all-reduce), then averaged over ranks by hand.  Prints one JSON line."""
+    from oracle import ref_port as orc                     # checker only (an example script, not the product path)
+    params = [p for p in model.parameters() if p.requires_grad]
+    for p in params:
+        p.grad = None
+    criterion.export_assignment = True                     # keep the CUDA path's decoded boxes: the oracle's assigner is fed
+    preds = net(img)                                       # with them (spliced oracle, SURVEY §4.2), so a 1-ulp decode
+    loss, items = criterion(preds, batch)                  # difference cannot flip a near-tie between two GT of one anchor
+    loss.backward()
+    boxes_px = criterion.last_export["pred_bboxes_px"].cpu()
+    g_ddp = [p.grad.detach().clone() for p in params]
+    for p in params:
+        p.grad = None
+    preds2 = model(img)                                    # same weights, no DDP hooks
+    leaves = [p.detach().cpu().requires_grad_(True) for p in preds2]
+    total, ritems = orc.detection_loss(leaves, {k: v.cpu() for k, v in batch.items()}, args.nc, 16, synth.LEVEL_STRIDES,
+                                       assign_boxes_px=boxes_px)
+    total.backward()
+    g_shard = torch.autograd.grad(preds2, params, grad_outputs=[l.grad.to(dev) for l in leaves], allow_unused=True)
+    g_shard = [torch.zeros_like(p) if g is None else g for g, p in zip(g_shard, params)]
+    if world > 1:
+        for g in g_shard:
+            dist.all_reduce(g, op=dist.ReduceOp.AVG)
+    num = sum(float((a - b).double().pow(2).sum()) for a, b in zip(g_ddp, g_shard)) ** 0.5
+    den = sum(float(b.double().pow(2).sum()) for b in g_shard) ** 0.5
+    worst = max(float((a - b).abs().max()) / (float(b.abs().max()) or 1.0) for a, b in zip(g_ddp, g_shard))
+    item_rel = float(((items.cpu() - ritems).abs() / ritems.abs().clamp_min(1e-12)).max())
+    ok = num / max(den, 1e-30) <= 1e-4 and item_rel <= 1e-5
+    res = torch.tensor([num / max(den, 1e-30), worst, item_rel, 1.0 if ok else 0.0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(res, op=dist.ReduceOp.MAX)
+        okt = torch.tensor([1.0 if ok else 0.0], device=dev)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        ok = bool(okt.item() > 0)
+    if rank == 0:
+        print(json.dumps({"check": "DDP-averaged parameter gradients vs mean over ranks of per-shard oracle gradients "
+                                   "(oracle/ref_port.detection_loss on each rank's head tensors, back-propagated through the "
+                                   "same graph)", "n_gpus": world, "model": f"YOLO11{args.scale}", "batch_per_gpu": args.batch,
+                          "imgsz": args.imgsz, "params": sum(p.numel() for p in params),
+                          "rel_l2_diff_all_params": float(res[0]), "worst_single_param_rel_max_diff": float(res[1]),
+                          "note": "the worst single parameter is one whose true gradient is zero (a conv bias in front of "
+                                  "BatchNorm): rounding noise over rounding noise; the all-parameter L2 figure is the check",
+                          "loss_items_rel_diff_max_over_ranks": float(res[2]), "ok": ok}), flush=True)
+    assert ok, "DDP gradients differ from the per-shard oracle mean"
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--scale", default="s")
@@ -43,8 +94,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--channels-last", action="store_true")
     ap.add_argument("--bf16", action="store_true", help="autocast the backbone to bf16 (the loss path stays fp32)")
+    ap.add_argument("--check-grads", action="store_true",
+                    help="multi-GPU oracle (SURVEY §8e): one step; DDP's averaged parameter gradients must equal the mean "
+                         "over ranks of the gradients obtained by back-propagating each shard's ORACLE head gradients")
     args = ap.parse_args()
 
+    if args.check_grads:       # an exact comparison: no TF32 in the convolutions (its 10-bit mantissa is a 5e-4 noise floor)
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -66,6 +123,12 @@ def main():
     if args.channels_last:
         img = img.contiguous(memory_format=torch.channels_last)
     batch = {k: v.to(dev) for k, v in synth.make_gt_batch(args.batch, args.nc, 20, seed=200 + rank).items()}
+
+    if args.check_grads:
+        check_grads(args, net, model, criterion, img, batch, rank, world, dev)
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     loss_ms = []
 
