@@ -124,7 +124,7 @@ __device__ __forceinline__ float score_at(const AssignIO &io, const LevelSet &L,
         int i = a - L.a_off[l];
         int hw = L.hw[l];
         float x = __ldg(L.x[l] + ((size_t)b * L.C + (L.C - io.nc) + label) * hw + i);
-        return sigmoidf(x);
+        return sigmoid_fast(x);
     } else {
         return __ldg(io.pd_scores + ((size_t)b * L.A + a) * io.nc + label);
     }
@@ -669,7 +669,12 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     __syncthreads();
     YS_BSTAMP(6);
     if (tid == 0) {
+#ifdef YS_ARRIVE_SC
         __threadfence();
+#else
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");      // release of the block's writes (the barrier ordered them before
+                                                              // this thread); lighter than the sequentially consistent membar
+#endif
         const unsigned prev = atomicAdd(&io.img_done[b], 1u);
         s_flag = (prev == gridDim.x - 1u);
     }

@@ -72,6 +72,19 @@ struct StreamMaps {
     CUtensorMap cls[YS_MAX_LEVELS];     // box {128 columns, 8 rows}
 };
 
+// Gradient stores of the streamed (written once, never re-read here) rows.  YS_STREAM_ST: 0 plain, 1 st.global.cs
+// (evict-first), 2 st.global.wt (write-through)
+#ifndef YS_STREAM_ST
+#define YS_STREAM_ST 0
+#endif
+#if YS_STREAM_ST == 1
+#define YS_ST4(p, v) __stcs((p), (v))
+#elif YS_STREAM_ST == 2
+#define YS_ST4(p, v) __stwt((p), (v))
+#else
+#define YS_ST4(p, v) (*(p) = (v))
+#endif
+
 // ---- mbarrier / bulk-copy primitives (PTX ISA: mbarrier, cp.async.bulk) ------------------------------------
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
@@ -238,7 +251,7 @@ __device__ __forceinline__ void stream_box_zero(const LevelSet &L, const Item &i
         if (col < it.n_live) {
             const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int c = 0; c < 8; ++c) *reinterpret_cast<float4 *>(g + (size_t)(c * 8 + rsub) * it.hw + col) = z4;
+            for (int c = 0; c < 8; ++c) YS_ST4(reinterpret_cast<float4 *>(g + (size_t)(c * 8 + rsub) * it.hw + col), z4);
         }
     } else {
         // rows without 16-byte alignment: 16 lanes per row, 2 rows per instruction, scalar stores
@@ -394,7 +407,7 @@ __device__ __forceinline__ void stream_cls(const LevelSet &L, const StreamParams
     auto row = [&](int c) {
         if (ALIGNED) {
             const float4 o = one(*reinterpret_cast<const float4 *>(tile + c * kChunk + lane * 4));
-            if (WRITE_GRAD) *reinterpret_cast<float4 *>(gc + (size_t)c * it.hw + lane * 4) = o;
+            if (WRITE_GRAD) YS_ST4(reinterpret_cast<float4 *>(gc + (size_t)c * it.hw + lane * 4), o);
         } else {
             const float *tr = tile + c * kChunk;
             const float4 o = one(make_float4(v0 ? tr[a0] : ninf, v1 ? tr[a1] : ninf, v2 ? tr[a2] : ninf, v3 ? tr[a3] : ninf));

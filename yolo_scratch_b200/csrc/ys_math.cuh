@@ -106,7 +106,6 @@ YS_HD float align_norm(float score, float ov, float alpha, float beta, float eps
 }
 
 YS_HD float sigmoidf(float x) { return 1.0f / (1.0f + expf(-x)); }
-
 // Order-preserving key for "max value, lowest index wins": (value bits << 32) | ~index.  value >= 0.
 YS_HD unsigned long long argmax_key(float v, unsigned idx) {
 #ifdef __CUDA_ARCH__
@@ -206,6 +205,14 @@ YS_HD float rcp_fast(float a) {
 #endif
 }
 
+// sigmoid by one ex2 and one rcp (+ a Newton step): relative error ~1e-7, tolerance section only
+YS_HD float sigmoid_fast(float x) {
+    const float e = ex2_fast(-x * kLog2e);
+    const float s = 1.0f + e;
+    const float r = rcp_fast(s);
+    return e < 3.0e38f ? r * fmaf(-s, r, 2.0f) : 0.0f;      // exp overflow: 1/inf = 0 (the Newton step would give NaN)
+}
+
 // log1p(e)/e on e in [0,1]: degree-7 minimax polynomial (Lawson fit; max relative error of e*P(e) vs log1p(e)
 // 3.7e-7 in fp32 Horner form, -1.6e-7 as e -> 0).  No MUFU, no branch.
 YS_HD float log1p_over_e(float e) {
@@ -245,7 +252,9 @@ YS_HD float dfl_stats16(const float (&z)[16], float &m2, float &inv_s) {
         d = fmaf(e, (float)j, d);
     }
     m2 = mm;
-    inv_s = 1.0f / s;
+    // 1/s: one MUFU + one Newton step (the IEEE division was the longest dependency chain of the decode; s is in [1, 16])
+    const float r = rcp_fast(s);
+    inv_s = r * fmaf(-s, r, 2.0f);
     return d * inv_s;
 }
 
