@@ -275,9 +275,10 @@ __global__ void __launch_bounds__(kSupThreads)
 k_nms_suppress(const int *__restrict__ count, int A, const float4 *__restrict__ sbox, const float *__restrict__ sscore,
                const int *__restrict__ scls, const int *__restrict__ sanchor, float thr, float img_size, int smem_boxes,
                int *__restrict__ keep_anchor, float4 *__restrict__ keep_boxes, float *__restrict__ keep_scores,
-               int *__restrict__ keep_labels, int *__restrict__ keep_count) {
+               int *__restrict__ keep_labels, int *__restrict__ keep_count, const int *__restrict__ only) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int b = blockIdx.x;
+    if (only && !only[b]) return;      // k_nms_suppress_grid has done this image
     const int n = count[b];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (n == 0) {
@@ -445,8 +446,9 @@ __global__ void __launch_bounds__(kRegThreads, 1)
 k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restrict__ sbox, const float *__restrict__ sscore,
                     const int *__restrict__ scls, const int *__restrict__ sanchor, float thr, float img_size,
                     int *__restrict__ keep_anchor, float4 *__restrict__ keep_boxes, float *__restrict__ keep_scores,
-                    int *__restrict__ keep_labels, int *__restrict__ keep_count) {
+                    int *__restrict__ keep_labels, int *__restrict__ keep_count, const int *__restrict__ only) {
     constexpr int kWarps = kRegThreads / 32;
+    if (only && !only[blockIdx.x]) return;      // k_nms_suppress_grid has done this image
     __shared__ float4 s_tile[64];
     __shared__ float s_tarea[64];
     __shared__ int s_tcls[64];
@@ -781,10 +783,301 @@ k_nms_suppress_zreg(const int *__restrict__ count, int A, const float4 *__restri
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// k_nms_suppress_grid: exact greedy NMS without the N^2 pair sweep.
+// Greedy NMS keeps box j iff no KEPT box i of higher score has IoU(i, j) > thr (train_yolo11_cuda.py:361-399).  Two facts
+// make that cheap: (1) IoU > thr forces the centres close -- inter > thr * union >= thr * area_a and inter_h <= h_a give
+// inter_w > thr * w_a (same for b), and inter_w <= (w_a + w_b) / 2 - |dcx|, so |dcx| < (1 - thr) * max(w_a, w_b)
+// (same in y): every possible suppressor of j lies within R = (1 - thr) * (largest box side of the image) of its centre;
+// (2) the verdict on j only needs the verdicts on those few neighbours.  So: the image's sorted candidates are binned
+// by centre into a 32 x 32 grid (counting sort in shared memory), and the keep flags are resolved in rounds: an
+// undecided box scans the cells within R for higher-ranked boxes with IoU > thr (the reference's exact arithmetic) --
+// one of them kept: removed; one of them undecided: wait for the next round; otherwise kept.  The lowest-ranked
+// undecided box always decides, so the rounds terminate, and the fixed point is the sequential greedy result.
+// With COCO-like boxes a scan meets ~1 % of the image's candidates and almost every box decides in the first round.
+// One block per image, everything in shared memory.  Images this kernel does not take -- non-finite or inverted boxes,
+// thr outside [0, 1), more candidates than fit, a search window wider than half the grid (one huge box), or a chain of
+// dependencies longer than kGridMaxRounds -- are flagged in `fallback` and done by the tile kernels below.
+// ---------------------------------------------------------------------------------------------------
+constexpr int kGridThreads = 1024;
+constexpr int kGridDim = 64;                 // cells per axis
+constexpr int kGridCells = kGridDim * kGridDim;
+constexpr int kGridMaxN = 8704;              // candidates per image held in shared memory
+constexpr int kGridMaxRounds = 96;
+#ifndef YS_NMS_GRID_MAX_WINDOW
+#define YS_NMS_GRID_MAX_WINDOW 130
+#endif
+constexpr int kGridMaxWindow = YS_NMS_GRID_MAX_WINDOW;   // mean candidates per search window above which the tile kernel takes the image
+constexpr int kCellsPerThread = kGridCells / kGridThreads;
+static_assert(kGridCells % kGridThreads == 0, "the cell prefix sum gives every thread the same number of cells");
+static_assert(kGridMaxN < (1 << 14), "rank and state share 16 bits");
+
+// shared memory: boxes in cell order (16 B) | rank + state (2 B) | class (1 B, class-aware) | first position of every cell
+// (+1) | two lists of undecided positions (the scatter cursors alias them) | kept bit per rank
+static size_t grid_smem_bytes(int n_cap, bool class_aware) {
+    const size_t lists = (size_t)2 * n_cap * 2, cursors = (size_t)kGridCells * 4;
+    return (size_t)n_cap * (16 + 2 + (class_aware ? 1 : 0)) + 16 + (size_t)(kGridCells + 1) * 4 + 16 +
+           (lists > cursors ? lists : cursors) + 16 + (size_t)((n_cap + 31) / 32) * 4 + 64;
+}
+
+template <bool CLASS_AWARE>
+__global__ void __launch_bounds__(kGridThreads, 1)
+k_nms_suppress_grid(const int *__restrict__ count, int A, const float4 *__restrict__ sbox, const float *__restrict__ sscore,
+                    const int *__restrict__ scls, const int *__restrict__ sanchor, float thr, float img_size, int n_cap,
+                    int *__restrict__ keep_anchor, float4 *__restrict__ keep_boxes, float *__restrict__ keep_scores,
+                    int *__restrict__ keep_labels, int *__restrict__ keep_count, int *__restrict__ fallback) {
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    constexpr int kWarps = kGridThreads / 32;
+    constexpr unsigned kRankMask = 0x3FFFu, kKept = 1u << 14, kRemoved = 2u << 14;      // state in the two top bits of s_rs
+    auto align16 = [](void *p) { return reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(p) + 15) & ~(uintptr_t)15); };
+    float4 *s_box = reinterpret_cast<float4 *>(s_raw);                                  // [n_cap] in cell order
+    unsigned short *s_rs = reinterpret_cast<unsigned short *>(s_box + n_cap);           // [n_cap] score rank | state << 14
+    unsigned char *s_cls = reinterpret_cast<unsigned char *>(s_rs + n_cap);             // [n_cap] (class-aware only)
+    int *s_cell = reinterpret_cast<int *>(align16(s_cls + (CLASS_AWARE ? n_cap : 0)));  // [cells + 1] first position of a cell
+    int *s_cursor = reinterpret_cast<int *>(align16(s_cell + kGridCells + 1));          // [cells] histogram / scatter cursors ...
+    unsigned short *s_list0 = reinterpret_cast<unsigned short *>(s_cursor);             // ... then: undecided positions, two buffers
+    unsigned short *s_list1 = s_list0 + n_cap;
+    const size_t lists = (size_t)2 * n_cap * 2, cursors = (size_t)kGridCells * 4;
+    unsigned *s_alive = reinterpret_cast<unsigned *>(align16(reinterpret_cast<unsigned char *>(s_cursor) + (lists > cursors ? lists : cursors)));
+    __shared__ float s_red[7][kWarps];
+    __shared__ int s_part[kWarps];
+    __shared__ int s_nlist[2];
+    const int b = blockIdx.x;
+    const int n = count[b];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (n == 0) {
+        if (tid == 0) { keep_count[b] = 0; fallback[b] = 0; }
+        return;
+    }
+    const float4 *gbox = sbox + (size_t)b * A;
+    const int *gcls = scls + (size_t)b * A;
+    const float pinf = __int_as_float(0x7f800000), ninf = __int_as_float(0xff800000);
+    // ---- pass 1 (rank order): sanity, extent of the (doubled) centres, largest width / height, largest |coordinate|
+    bool sane = n <= n_cap && thr >= 0.f && thr < 1.f;
+    float mnx = pinf, mny = pinf, mxx = ninf, mxy = ninf, wmax = 0.f, hmax = 0.f, big = 0.f;
+    if (sane) {
+        for (int r = tid; r < n; r += kGridThreads) {
+            const float4 v = gbox[r];
+            const float w = v.z - v.x, h = v.w - v.y;
+            sane = sane && (w >= 0.f) && (h >= 0.f) && (fabsf(v.x) + fabsf(v.y) + fabsf(v.z) + fabsf(v.w) < 1.0e18f);
+            if (CLASS_AWARE) sane = sane && ((unsigned)gcls[r] < 256u);
+            const float sx = v.x + v.z, sy = v.y + v.w;
+            mnx = fminf(mnx, sx); mxx = fmaxf(mxx, sx);
+            mny = fminf(mny, sy); mxy = fmaxf(mxy, sy);
+            wmax = fmaxf(wmax, w); hmax = fmaxf(hmax, h);
+            big = fmaxf(big, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+        }
+    }
+    auto wred = [&]() {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mnx = fminf(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mny = fminf(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+            mxx = fmaxf(mxx, __shfl_xor_sync(0xffffffffu, mxx, o)); mxy = fmaxf(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+            wmax = fmaxf(wmax, __shfl_xor_sync(0xffffffffu, wmax, o)); hmax = fmaxf(hmax, __shfl_xor_sync(0xffffffffu, hmax, o));
+            big = fmaxf(big, __shfl_xor_sync(0xffffffffu, big, o));
+        }
+    };
+    wred();
+    if (lane == 0) { s_red[0][warp] = mnx; s_red[1][warp] = mny; s_red[2][warp] = mxx; s_red[3][warp] = mxy; s_red[4][warp] = wmax; s_red[5][warp] = hmax; s_red[6][warp] = big; }
+    for (int i = tid; i < kGridCells; i += kGridThreads) s_cursor[i] = 0;
+    sane = __syncthreads_and(sane);
+    mnx = s_red[0][lane]; mny = s_red[1][lane]; mxx = s_red[2][lane]; mxy = s_red[3][lane]; wmax = s_red[4][lane]; hmax = s_red[5][lane]; big = s_red[6][lane];
+    wred();
+    // Search radii in doubled-centre units (see the note above the kernel): per axis min((1 - thr) * largest side of the image,
+    // (1 - thr) / thr * own side) -- IoU > thr also bounds the partner's side by own side / thr -- with 1 % of slack for the
+    // reference's fp32 rounding of the IoU (its +1e-6 in the denominator only lowers it) and an absolute term for the
+    // rounding of the centre sums.
+    const float kf = 1.0f - thr + 0.01f, slack = 4.0e-6f * big;
+    const float kown = thr > 0.f ? 2.0f * kf / thr : pinf;
+    const float R2xg = 2.0f * kf * wmax + slack, R2yg = 2.0f * kf * hmax + slack;
+    const float gsx = (mxx > mnx) ? (float)kGridDim / (mxx - mnx) : 0.f;
+    const float gsy = (mxy > mny) ? (float)kGridDim / (mxy - mny) : 0.f;
+    // a window wider than half the grid (one huge box, or everything in one spot) is no pruning at all
+    const bool wide = (gsx > 0.f && R2xg * gsx > 0.25f * kGridDim) || (gsy > 0.f && R2yg * gsy > 0.25f * kGridDim) ||
+                      (gsx == 0.f && gsy == 0.f && n > 256);
+    if (!sane || wide) {              // block-uniform
+        if (tid == 0) fallback[b] = 1;
+        return;
+    }
+    auto cell_x = [&](float c2) { return min(max((int)((c2 - mnx) * gsx), 0), kGridDim - 1); };
+    auto cell_y = [&](float c2) { return min(max((int)((c2 - mny) * gsy), 0), kGridDim - 1); };
+    // ---- counting sort by cell
+    for (int r = tid; r < n; r += kGridThreads) {
+        const float4 v = gbox[r];
+        atomicAdd(&s_cursor[cell_y(v.y + v.w) * kGridDim + cell_x(v.x + v.z)], 1);
+    }
+    __syncthreads();
+    {   // exclusive prefix over the cells: kCellsPerThread consecutive cells per thread
+        int v[kCellsPerThread], tot = 0;
+#pragma unroll
+        for (int j = 0; j < kCellsPerThread; ++j) { v[j] = s_cursor[tid * kCellsPerThread + j]; tot += v[j]; }
+        int inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_part[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            const int pv = s_part[lane];
+            int pi = pv;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, pi, o);
+                if (lane >= o) pi += t;
+            }
+            s_part[lane] = pi - pv;
+        }
+        __syncthreads();
+        int run = s_part[warp] + inc - tot;
+#pragma unroll
+        for (int j = 0; j < kCellsPerThread; ++j) {
+            s_cell[tid * kCellsPerThread + j] = run;
+            s_cursor[tid * kCellsPerThread + j] = run;
+            run += v[j];
+        }
+        if (tid == kGridThreads - 1) s_cell[kGridCells] = run;
+    }
+    __syncthreads();
+    for (int r = tid; r < n; r += kGridThreads) {
+        const float4 v = gbox[r];
+        const int p = atomicAdd(&s_cursor[cell_y(v.y + v.w) * kGridDim + cell_x(v.x + v.z)], 1);
+        s_box[p] = v;
+        s_rs[p] = (unsigned short)r;                 // state 0: undecided
+        if (CLASS_AWARE) s_cls[p] = (unsigned char)gcls[r];
+    }
+    if (tid == 0) { s_nlist[0] = 0; s_nlist[1] = 0; s_part[0] = 0; }
+    __syncthreads();                                  // the cursors are dead from here: their memory holds the lists
+    // ---- is the image sparse enough?  The scan below visits every candidate of a box's window; dense scenes (boxes jittered
+    //      around a few centres, low thresholds) have hundreds of candidates per window and are better served by the tile
+    //      kernel, whose cost does not depend on the density.  The window populations come from the cell table for free.
+    {
+        long long pop = 0;
+        for (int p = tid; p < n; p += kGridThreads) {
+            const float4 a = s_box[p];
+            const float c2x = a.x + a.z, c2y = a.y + a.w;
+            const float R2x = fminf(R2xg, kown * (a.z - a.x) + slack), R2y = fminf(R2yg, kown * (a.w - a.y) + slack);
+            const int cx0 = cell_x(c2x - R2x), cx1 = cell_x(c2x + R2x), cy0 = cell_y(c2y - R2y), cy1 = cell_y(c2y + R2y);
+            for (int cy = cy0; cy <= cy1; ++cy) pop += s_cell[cy * kGridDim + cx1 + 1] - s_cell[cy * kGridDim + cx0];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) pop += __shfl_xor_sync(0xffffffffu, pop, o);
+        if (lane == 0) atomicAdd(&s_part[0], (int)min(pop, (long long)0x3fffff));
+        __syncthreads();
+        if ((long long)s_part[0] > (long long)kGridMaxWindow * n) {      // block-uniform
+            if (tid == 0) fallback[b] = 1;
+            return;
+        }
+    }
+    // ---- rounds.  Round 0 walks every position; later rounds only the positions still undecided (compacted lists).
+    volatile unsigned short *rs = s_rs;
+    int rounds = 0;
+    bool gave_up = false;
+    while (true) {
+        const unsigned short *lin = (rounds & 1) ? s_list0 : s_list1;        // written by the previous round
+        unsigned short *lout = (rounds & 1) ? s_list1 : s_list0;
+        int *nout = &s_nlist[rounds & 1 ? 1 : 0];
+        const int nin = rounds == 0 ? n : s_nlist[rounds & 1 ? 0 : 1];
+        for (int i = tid; i < nin; i += kGridThreads) {
+            const int p = rounds == 0 ? i : (int)lin[i];
+            const float4 a = s_box[p];
+            const unsigned ra = rs[p] & kRankMask;
+            const float c2x = a.x + a.z, c2y = a.y + a.w;
+            const float R2x = fminf(R2xg, kown * (a.z - a.x) + slack), R2y = fminf(R2yg, kown * (a.w - a.y) + slack);
+            const int cx0 = cell_x(c2x - R2x), cx1 = cell_x(c2x + R2x), cy0 = cell_y(c2y - R2y), cy1 = cell_y(c2y + R2y);
+            const float area_a = area_plain(a);
+            const int cls_a = CLASS_AWARE ? (int)s_cls[p] : 0;
+            bool removed = false, pending = false;
+            for (int cy = cy0; cy <= cy1 && !removed; ++cy) {
+                const int q1 = s_cell[cy * kGridDim + cx1 + 1];
+                for (int q = s_cell[cy * kGridDim + cx0]; q < q1; ++q) {
+                    const unsigned rq = rs[q];
+                    if ((rq & kRankMask) >= ra) continue;                  // only higher-scored boxes can suppress
+                    if (rq & kRemoved) continue;                           // a removed box suppresses nobody
+                    if (CLASS_AWARE && (int)s_cls[q] != cls_a) continue;
+                    const float4 e = s_box[q];
+                    const float iw = YS_SUB(fminf2(e.z, a.z), fmaxf2(e.x, a.x));
+                    const float ih = YS_SUB(fminf2(e.w, a.w), fmaxf2(e.y, a.y));
+                    if (!(iw > 0.f) || !(ih > 0.f)) continue;              // sane boxes: IoU is exactly 0 (thr >= 0)
+                    // iou_nms(e, a) > thr with the reference's arithmetic (train_yolo11_cuda.py:418-435, :396)
+                    const float inter = YS_MUL(iw, ih);
+                    const float den = YS_ADD(YS_SUB(YS_ADD(area_plain(e), area_a), inter), kEpsNms);
+                    if (YS_DIV(inter, den) <= thr) continue;
+                    if (rq & kKept) { removed = true; break; }
+                    pending = true;                                        // undecided when read (it may have been decided since:
+                }                                                          // then the next round sees it)
+            }
+            if (removed) rs[p] = (unsigned short)(ra | kRemoved);
+            else if (!pending) rs[p] = (unsigned short)(ra | kKept);
+            else lout[atomicAdd(nout, 1)] = (unsigned short)p;
+        }
+        __syncthreads();
+        const int left = *nout;
+        if (left == 0) break;
+        if (++rounds >= kGridMaxRounds) { gave_up = true; break; }
+        if (tid == 0) s_nlist[rounds & 1 ? 1 : 0] = 0;                    // the list this coming round appends to
+        __syncthreads();
+    }
+#ifdef YS_NMS_GRID_DEBUG
+    if (tid == 0 && b < 6) printf("GRID b=%d n=%d rounds=%d gave_up=%d R2xg=%.1f cells=%.2f left=%d\n", b, n, rounds, (int)gave_up, R2xg, R2xg * gsx, *(&s_nlist[rounds & 1 ? 1 : 0]));
+#endif
+    if (gave_up) {                    // block-uniform: a long dependency chain; the tile kernel redoes this image
+        if (tid == 0) fallback[b] = 1;
+        return;
+    }
+    // ---- survivors: rank-indexed bitmap, per-word offsets from one popcount scan, all warps write
+    for (int i = tid; i < (n + 31) / 32; i += kGridThreads) s_alive[i] = 0u;
+    __syncthreads();
+    for (int p = tid; p < n; p += kGridThreads) {
+        const unsigned v = s_rs[p];
+        if (v & kKept) atomicOr(&s_alive[(v & kRankMask) >> 5], 1u << (v & 31u));
+    }
+    __syncthreads();
+    int *s_base = s_cursor;                                        // the lists are free now
+    const int nwords = (n + 31) >> 5;
+    if (warp == 0) {
+        int running = 0;
+        for (int w0 = 0; w0 < nwords; w0 += 32) {
+            const int w = w0 + lane;
+            const int cnt = w < nwords ? __popc(s_alive[w]) : 0;
+            int inc = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            if (w < nwords) s_base[w] = running + inc - cnt;
+            running += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (lane == 0) { keep_count[b] = running; fallback[b] = 0; }
+    }
+    __syncthreads();
+    for (int w = warp; w < nwords; w += kWarps) {
+        const unsigned m = s_alive[w];
+        if ((m >> lane) & 1u) {
+            const size_t o = (size_t)b * A + s_base[w] + __popc(m & ((1u << lane) - 1u));
+            const size_t src = (size_t)b * A + w * 32 + lane;
+            if (keep_anchor) keep_anchor[o] = sanchor[src];
+            if (keep_boxes) {
+                const float4 v = sbox[src];
+                // boxes / img_size, clamp to [0,1]  (train_yolo11_cuda.py:347-350)
+                float4 q = make_float4(YS_DIV(v.x, img_size), YS_DIV(v.y, img_size), YS_DIV(v.z, img_size), YS_DIV(v.w, img_size));
+                q.x = fminf2(fmaxf2(q.x, 0.f), 1.f); q.y = fminf2(fmaxf2(q.y, 0.f), 1.f);
+                q.z = fminf2(fmaxf2(q.z, 0.f), 1.f); q.w = fminf2(fmaxf2(q.w, 0.f), 1.f);
+                keep_boxes[o] = q;
+            }
+            if (keep_scores) keep_scores[o] = sscore[src];
+            if (keep_labels) keep_labels[o] = scls[src];
+        }
+    }
+}
+
 struct NmsWorkspace {
     unsigned long long *keys, *keys2;      // keys2: segment-sorted keys, only when A > kSortMaxN
     float4 *boxes, *sbox;
-    int *cls, *scls, *sanchor, *count;
+    int *cls, *scls, *sanchor, *count, *fallback;
     float *sscore;
     size_t bytes;
 };
@@ -792,6 +1085,7 @@ static void carve_nms(NmsWorkspace &W, void *base, size_t cap, int B, int A) {
     Carver c(base, cap);
     const size_t n = (size_t)B * A;
     W.count = c.take<int>((size_t)B + 1);
+    W.fallback = c.take<int>((size_t)B + 1);
     W.keys = c.take<unsigned long long>(n);
     W.keys2 = A > kSortMaxN ? c.take<unsigned long long>(n) : nullptr;
     W.boxes = c.take<float4>(n);
@@ -835,11 +1129,31 @@ static int run_sort_suppress(const NmsWorkspace &W, int B, int A, float iou_thr,
         k_nms_merge<<<dim3((A + 255) / 256, B), 256, 0, stream>>>(W.keys2, W.count, A, boxes, cls, W.sbox, W.sscore, W.scls, W.sanchor);
         YS_CHECK_LAUNCH("k_nms_merge");
     }
+    // Grid kernel first (every image it can take); the tile kernels then run for the images it flagged only.
+    const int *only = nullptr;
+#ifndef YS_NMS_NO_GRID
+    if (A <= kGridMaxN) {
+        static DeviceOnce once_grid[2];
+        const int n_cap = (A + 31) & ~31;
+        const size_t gsm = grid_smem_bytes(n_cap, class_aware != 0);
+        rc = class_aware ? optin_smem((const void *)k_nms_suppress_grid<true>, grid_smem_bytes(kGridMaxN, true), once_grid[1], "k_nms_suppress_grid")
+                         : optin_smem((const void *)k_nms_suppress_grid<false>, grid_smem_bytes(kGridMaxN, false), once_grid[0], "k_nms_suppress_grid");
+        if (rc) return rc;
+        if (class_aware)
+            k_nms_suppress_grid<true><<<B, kGridThreads, gsm, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr, img_size, n_cap,
+                                                                         keep_anchor, (float4 *)keep_boxes, keep_scores, keep_labels, keep_count, W.fallback);
+        else
+            k_nms_suppress_grid<false><<<B, kGridThreads, gsm, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr, img_size, n_cap,
+                                                                          keep_anchor, (float4 *)keep_boxes, keep_scores, keep_labels, keep_count, W.fallback);
+        YS_CHECK_LAUNCH("k_nms_suppress_grid");
+        only = W.fallback;
+    }
+#endif
     if (A <= 9 * kRegThreads) {      // register-resident columns (every 640 px / 8400-candidate case)
 #define YS_LAUNCH_REG(CA, COLS)                                                                                              \
     k_nms_suppress_zreg<CA, COLS><<<B, kRegThreads, 0, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr,      \
                                                                 img_size, keep_anchor, (float4 *)keep_boxes, keep_scores,     \
-                                                                keep_labels, keep_count)
+                                                                keep_labels, keep_count, only)
         if (A <= 2 * kRegThreads) { if (class_aware) YS_LAUNCH_REG(true, 2); else YS_LAUNCH_REG(false, 2); }
         else if (A <= 5 * kRegThreads) { if (class_aware) YS_LAUNCH_REG(true, 5); else YS_LAUNCH_REG(false, 5); }
         else { if (class_aware) YS_LAUNCH_REG(true, 9); else YS_LAUNCH_REG(false, 9); }
@@ -851,10 +1165,10 @@ static int run_sort_suppress(const NmsWorkspace &W, int B, int A, float iou_thr,
     const size_t sup_smem = suppress_smem_bytes(A, smem_boxes);
     if (class_aware)
         k_nms_suppress<true><<<B, kSupThreads, sup_smem, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr, img_size,
-                                                                   smem_boxes, keep_anchor, (float4 *)keep_boxes, keep_scores, keep_labels, keep_count);
+                                                                   smem_boxes, keep_anchor, (float4 *)keep_boxes, keep_scores, keep_labels, keep_count, only);
     else
         k_nms_suppress<false><<<B, kSupThreads, sup_smem, stream>>>(W.count, A, W.sbox, W.sscore, W.scls, W.sanchor, iou_thr, img_size,
-                                                                    smem_boxes, keep_anchor, (float4 *)keep_boxes, keep_scores, keep_labels, keep_count);
+                                                                    smem_boxes, keep_anchor, (float4 *)keep_boxes, keep_scores, keep_labels, keep_count, only);
     YS_CHECK_LAUNCH("k_nms_suppress");
     return YS_OK;
 }
