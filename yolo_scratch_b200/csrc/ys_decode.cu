@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer(LevelSet L, int nc
 #pragma unroll 4
         for (int c = c_lo; c < c_hi; ++c) {
             const float4 xv = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)c * hw));
-            const float4 s = make_float4(sigmoidf(xv.x), sigmoidf(xv.y), sigmoidf(xv.z), sigmoidf(xv.w));
+            const float4 s = make_float4(sigmoid_fast(xv.x), sigmoid_fast(xv.y), sigmoid_fast(xv.z), sigmoid_fast(xv.w));
             if (LAYOUT == 0) {
                 *reinterpret_cast<float4 *>(out + ((size_t)b * R + 4 + c) * A + a0) = s;
             } else {
@@ -96,7 +96,13 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer(LevelSet L, int nc
         const int rows = min(kChunk, hw - c0);
         float *dst = out + ((size_t)b * A + L.a_off[l] + c0) * R;
         const int total = rows * R;
-        for (int i = tid; i < total; i += kDecThreads) dst[i] = s_out[i];
+        if (((total | R) & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {      // the block's rows are one aligned run
+            const float4 *s4 = reinterpret_cast<const float4 *>(s_out);
+            float4 *d4 = reinterpret_cast<float4 *>(dst);
+            for (int i = tid; i < (total >> 2); i += kDecThreads) d4[i] = s4[i];
+        } else {
+            for (int i = tid; i < total; i += kDecThreads) dst[i] = s_out[i];
+        }
     }
 }
 
@@ -146,7 +152,7 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer_any(LevelSet L, in
         }
         const float *xc = xin + (size_t)64 * hw;
         for (int c = 0; c < nc; ++c) {
-            const float sg = sigmoidf(__ldg(xc + (size_t)c * hw));
+            const float sg = sigmoid_fast(__ldg(xc + (size_t)c * hw));
             if (LAYOUT == 0) out[((size_t)b * R + 4 + c) * A + a] = sg;
             else s_out[(size_t)tid * R + 4 + c] = sg;
         }
