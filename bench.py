@@ -301,6 +301,8 @@ def run_b200(args):
     side = torch.cuda.Stream(dev)
     graph, timing_mode = None, "cuda graph of K steps, replayed per window"
     try:
+        if args.no_graph:
+            raise RuntimeError("--no-graph")
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph, stream=side):
             for _ in range(args.steps):
@@ -571,6 +573,7 @@ def main():
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU legs (cpu_baseline, parity_check, c1, nms CPU)")
     ap.add_argument("--no-nms", action="store_true", help="skip the NMS and decode side measurements")
+    ap.add_argument("--no-graph", action="store_true", help="eager launches in the timed windows (profiling under ncu)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

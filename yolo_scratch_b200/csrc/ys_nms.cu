@@ -988,26 +988,33 @@ k_nms_suppress_grid(const int *__restrict__ count, int A, const float4 *__restri
             const float R2x = fminf(R2xg, kown * (a.z - a.x) + slack), R2y = fminf(R2yg, kown * (a.w - a.y) + slack);
             const int cx0 = cell_x(c2x - R2x), cx1 = cell_x(c2x + R2x), cy0 = cell_y(c2y - R2y), cy1 = cell_y(c2y + R2y);
             const float area_a = area_plain(a);
+            const float tw_a = fmaxf(0.99f * thr * (a.z - a.x), 0.f), th_a = fmaxf(0.99f * thr * (a.w - a.y), 0.f);
             const int cls_a = CLASS_AWARE ? (int)s_cls[p] : 0;
             bool removed = false, pending = false;
             for (int cy = cy0; cy <= cy1 && !removed; ++cy) {
                 const int q1 = s_cell[cy * kGridDim + cx1 + 1];
                 for (int q = s_cell[cy * kGridDim + cx0]; q < q1; ++q) {
+                    // straight-line candidate test (no early `continue`s: a warp's lanes walk different candidates, and
+                    // every divergent exit was being executed by the whole warp): higher-scored, not removed, same class,
+                    // and -- IoU > thr needs inter_w > thr * own width and inter_h > thr * own height (see the note above
+                    // the kernel; 1 % of slack for the reference's fp32 rounding) -- two compares that settle almost every pair
                     const unsigned rq = rs[q];
-                    if ((rq & kRankMask) >= ra) continue;                  // only higher-scored boxes can suppress
-                    if (rq & kRemoved) continue;                           // a removed box suppresses nobody
-                    if (CLASS_AWARE && (int)s_cls[q] != cls_a) continue;
                     const float4 e = s_box[q];
                     const float iw = YS_SUB(fminf2(e.z, a.z), fmaxf2(e.x, a.x));
                     const float ih = YS_SUB(fminf2(e.w, a.w), fmaxf2(e.y, a.y));
-                    if (!(iw > 0.f) || !(ih > 0.f)) continue;              // sane boxes: IoU is exactly 0 (thr >= 0)
-                    // iou_nms(e, a) > thr with the reference's arithmetic (train_yolo11_cuda.py:418-435, :396)
-                    const float inter = YS_MUL(iw, ih);
-                    const float den = YS_ADD(YS_SUB(YS_ADD(area_plain(e), area_a), inter), kEpsNms);
-                    if (YS_DIV(inter, den) <= thr) continue;
-                    if (rq & kKept) { removed = true; break; }
-                    pending = true;                                        // undecided when read (it may have been decided since:
-                }                                                          // then the next round sees it)
+                    bool cand = ((rq & kRankMask) < ra) & !(rq & kRemoved) & (iw > tw_a) & (ih > th_a);
+                    if (CLASS_AWARE) cand = cand & ((int)s_cls[q] == cls_a);
+                    if (cand) {
+                        // iou_nms(e, a) > thr with the reference's arithmetic (train_yolo11_cuda.py:418-435, :396); the
+                        // division only when the quotient could exceed thr (den > 0; fl(x / y) <= (x / y) * (1 + 2^-24))
+                        const float inter = YS_MUL(iw, ih);
+                        const float den = YS_ADD(YS_SUB(YS_ADD(area_plain(e), area_a), inter), kEpsNms);
+                        if (inter > __fmul_rn(0.999f * thr, den) && !(YS_DIV(inter, den) <= thr)) {
+                            if (rq & kKept) { removed = true; break; }
+                            pending = true;                                // undecided when read (it may have been decided
+                        }                                                  // since: then the next round sees it)
+                    }
+                }
             }
             if (removed) rs[p] = (unsigned short)(ra | kRemoved);
             else if (!pending) rs[p] = (unsigned short)(ra | kKept);
