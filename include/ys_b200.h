@@ -190,6 +190,21 @@ int ys_bbox_loss(const float *pred_dist, const float *pred_bboxes, const float *
                  const float *target_scores_sum, int n, int A, int nc, int reg_max, float *loss_out,
                  float *grad_pred_bboxes, float *grad_pred_dist, void *workspace, size_t workspace_bytes, void *stream);
 
+/* ys_bbox_loss without a caller workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments, results and error behaviour as ys_bbox_loss minus
+ * workspace / workspace_bytes; the kernel's scratch (arrival counter + per-block partial sums) is a file-scope
+ * __device__ array of 256 + 8 * YS_BBOX_LOSS_STATIC_MAX_ROWS / 64 bytes (128.25 KiB) that every GPU loading the library
+ * holds until exit.  n > YS_BBOX_LOSS_STATIC_MAX_ROWS returns YS_ERR_UNSUPPORTED (use ys_bbox_loss).  Calls no
+ * cudaMalloc / cudaFree or allocating library routine.  All calls on one device share the scratch: calls that overlap
+ * on the GPU (two streams, or a replaying graph next to an eager call) race; serialise them. */
+#define YS_BBOX_LOSS_STATIC_MAX_ROWS 1048576 /* n = B*A rows; B=64 at 1280 px (33600 anchors) is 2150400: use ys_bbox_loss */
+int ys_bbox_loss_static_max_rows(void);
+int ys_bbox_loss_static(const float *pred_dist, const float *pred_bboxes, const float *anchor_points,
+                        const float *target_bboxes, const float *target_scores, const uint8_t *fg_mask,
+                        const float *target_scores_sum, int n, int A, int nc, int reg_max, float *loss_out,
+                        float *grad_pred_bboxes, float *grad_pred_dist, void *stream);
+
 /* ---------------------------------------------------------------------------
  * Greedy detection-to-GT matching of evaluate_detections (utils/metrics.py:147-205, :211-256): per image,
  * predictions in score-descending order, each takes the best-IoU unmatched GT (first maximum, class agnostic); true

@@ -52,6 +52,8 @@ PROTOTYPES = {
     "ys_cda_nms": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, C.c_double, c_void_p, c_void_p, c_void_p]),
     "ys_bbox_loss_workspace_bytes": (c_size_t, [c_int]),
     "ys_bbox_loss": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p] * 3 + [c_void_p, c_size_t, c_void_p]),
+    "ys_bbox_loss_static_max_rows": (c_int, []),
+    "ys_bbox_loss_static": (c_int, [c_void_p] * 7 + [c_int] * 4 + [c_void_p] * 3 + [c_void_p]),
     "ys_bbox_iou": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
 }
 

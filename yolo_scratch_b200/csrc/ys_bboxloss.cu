@@ -166,3 +166,73 @@ extern "C" int ys_bbox_loss(const float *pred_dist, const float *pred_bboxes, co
     YS_CHECK_LAUNCH("k_bbox_loss");
     return YS_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// ys_bbox_loss_static: the same kernel for callers that cannot hand over a workspace they allocated (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The kernel's scratch -- the arrival counter and the per-block partial sums -- lives
+// in a file-scope __device__ array of a fixed, modest size that every GPU loading the library holds until exit.
+//
+// g_bbox_loss_scratch is, in HOST code, only a stand-in for the symbol: its device address is obtained once per device,
+// with that device current, through cudaGetSymbolAddress, and that address is what the kernel receives.
+// All calls on one device share the array: two calls that overlap on the GPU (different streams) race on it.  The arrival
+// counter must start at zero: the kernel's last block resets it, and it is cleared on the stream before every launch as
+// well (a cudaMemsetAsync on the symbol's address: no allocation), so a call that died mid-way cannot poison the next.
+// The partial sums need no clearing (every block writes its slot before the last block reads it).
+namespace ys {
+constexpr int kBlStaticMaxRows = YS_BBOX_LOSS_STATIC_MAX_ROWS;
+constexpr size_t kBlStaticBytes = 256 + ((size_t)kBlStaticMaxRows * 4 / kBlThreads) * sizeof(float2);
+static_assert(((size_t)kBlStaticMaxRows * 4) % kBlThreads == 0, "row limit must fill whole blocks");
+static __device__ __align__(256) unsigned char g_bbox_loss_scratch[kBlStaticBytes];
+
+// Device address of g_bbox_loss_scratch on the CURRENT device (cached per device in an atomic; a lost race repeats an
+// idempotent query).
+static int bbox_loss_static_scratch(void **out) {
+    static std::atomic<void *> cache[256];
+    int dev = 0;
+    cudaError_t ce = cudaGetDevice(&dev);
+    YS_REQUIRE(ce == cudaSuccess, (int)ce, "ys_bbox_loss_static: cudaGetDevice: %s", cudaGetErrorString(ce));
+    void *p = (dev >= 0 && dev < 256) ? cache[dev].load(std::memory_order_acquire) : nullptr;
+    if (!p) {
+        ce = cudaGetSymbolAddress(&p, g_bbox_loss_scratch);
+        YS_REQUIRE(ce == cudaSuccess && p != nullptr, (int)(ce ? ce : cudaErrorUnknown),
+                   "ys_bbox_loss_static: cudaGetSymbolAddress: %s", cudaGetErrorString(ce));
+        if (dev >= 0 && dev < 256) cache[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return YS_OK;
+}
+}  // namespace ys
+
+extern "C" int ys_bbox_loss_static_max_rows(void) { return kBlStaticMaxRows; }
+
+extern "C" int ys_bbox_loss_static(const float *pred_dist, const float *pred_bboxes, const float *anchor_points,
+                                   const float *target_bboxes, const float *target_scores, const uint8_t *fg_mask,
+                                   const float *target_scores_sum, int n, int A, int nc, int reg_max, float *loss_out,
+                                   float *grad_pred_bboxes, float *grad_pred_dist, void *stream_v) {
+    YS_REQUIRE(n >= 1 && A >= 1 && nc >= 1 && reg_max >= 1, YS_ERR_BAD_ARG, "n, A, nc, reg_max must be >= 1");
+    YS_REQUIRE(n <= kBlStaticMaxRows, YS_ERR_UNSUPPORTED,
+               "ys_bbox_loss_static: n = %d rows exceeds the built-in scratch (at most %d rows); use ys_bbox_loss with a "
+               "caller-provided workspace", n, kBlStaticMaxRows);
+    YS_REQUIRE(n % A == 0, YS_ERR_BAD_ARG, "n (%d) must be a multiple of the anchor count (%d)", n, A);
+    YS_REQUIRE(pred_dist && pred_bboxes && anchor_points && target_bboxes && target_scores && fg_mask && target_scores_sum &&
+                   loss_out, YS_ERR_BAD_ARG, "null pointer");
+    YS_REQUIRE((((uintptr_t)pred_bboxes | (uintptr_t)target_bboxes | (uintptr_t)grad_pred_bboxes) & 15) == 0 &&
+                   ((uintptr_t)anchor_points & 7) == 0, YS_ERR_BAD_ARG, "box pointers must be 16-byte aligned, anchor_points 8-byte");
+    void *scratch = nullptr;
+    const int rc = bbox_loss_static_scratch(&scratch);
+    if (rc != YS_OK) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    BboxLossArgs P;
+    P.pred_dist = pred_dist; P.pred_bboxes = (const float4 *)pred_bboxes; P.anchor_points = (const float2 *)anchor_points;
+    P.target_bboxes = (const float4 *)target_bboxes; P.target_scores = target_scores; P.fg_mask = fg_mask;
+    P.tss = target_scores_sum; P.loss_out = loss_out; P.grad_boxes = (float4 *)grad_pred_bboxes; P.grad_dist = grad_pred_dist;
+    P.done = (unsigned *)scratch;
+    P.partials = (float2 *)((char *)scratch + 256);
+    P.n = n; P.A = A; P.nc = nc; P.R = reg_max;
+    cudaError_t ce = cudaMemsetAsync(scratch, 0, 256, stream);
+    YS_REQUIRE(ce == cudaSuccess, (int)ce, "ys_bbox_loss_static: cudaMemsetAsync: %s", cudaGetErrorString(ce));
+    k_bbox_loss<<<bbox_loss_blocks(n), kBlThreads, 0, stream>>>(P);
+    YS_CHECK_LAUNCH("k_bbox_loss (static scratch)");
+    return YS_OK;
+}
