@@ -47,6 +47,11 @@ def test_detect_inference_640_then_nms_end_to_end(cuda_lib):
     ([(84, 84), (42, 42), (21, 21)], 80),      # imgsz 672: P5 = 441 = 1 mod 4
     ([(9, 7), (5, 3), (3, 1)], 5),             # every level unaligned
     ([(20, 28), (10, 14), (5, 7)], 6),         # non-square head, 35 = 3 mod 4
+    ([(16, 16), (8, 8), (4, 4)], 12),          # aligned levels, 4 + nc = 16: anchor-major rows staged with an odd pitch
+    ([(24, 24), (12, 12), (6, 6)], 20),        # aligned levels, 4 + nc = 24 = 0 mod 8
+    ([(13, 13), (7, 7), (4, 4)], 28),          # unaligned levels, 4 + nc = 32 = 0 mod 8: odd pitch
+    ([(13, 11), (7, 5), (4, 3)], 8),           # unaligned levels, 4 + nc = 12 = 4 mod 8: 16-byte staging words
+    ([(40, 40), (20, 20), (10, 10)], 3),       # nc not a multiple of 4: partial class group
 ])
 def test_detect_inference_unaligned_levels(cuda_lib, shapes, nc):
     """Head shapes the float4 kernel cannot take (the reference's Detect.inference accepts any image size,

@@ -92,6 +92,15 @@ def test_loss_dense_scene_vs_oracle(cuda_lib, seed, B, imgsz, kw):
     spliced_case(seed, B, imgsz, kw.get("fixed_count", 20), kw)
 
 
+def test_loss_many_images_mixed_counts_multiblock_pack(cuda_lib):
+    """More than 1024 GT spread over 64 images with 0..60 GT each (empty images in the middle and at the end): the
+    multi-block k_pack_gt's sorted path -- image boundaries found per row, gaps in gt_off filled, containment hint
+    from the halo'd rows -- against the oracle."""
+    batch = synth.make_gt_batch(64, 80, 60, seed=217, imgsz=320, p_empty=0.2, p_nested=0.3, p_tiny=0.1)
+    assert batch["cls"].shape[0] > 1024 and int(batch["batch_idx"].max()) < 63
+    spliced_case(216, 64, 320, 60, {"p_empty": 0.2, "p_nested": 0.3, "p_tiny": 0.1})
+
+
 @pytest.mark.parametrize("seed,nc", [(220, 1), (221, 13), (222, 23)])
 def test_loss_vs_oracle_other_class_counts(cuda_lib, seed, nc):
     """Class counts that are not a multiple of the class rows per work item (10): one partial group (nc = 1), a full

@@ -8,13 +8,10 @@ namespace ys {
 
 constexpr int kDecThreads = 128;
 
+// Channels-first output (B, 4+nc, A), what Detect.inference returns (models/yolo11_modules.py:263-266).
 // One block = 128 consecutive anchors of one level of one image; thread = 4 anchors; warp w = box side w and a
-// quarter of the classes (same decomposition as the loss kernel).
-// LAYOUT 0: out (B, 4+nc, A) -- per-channel float4 stores.
-// LAYOUT 1: out (B, A, 4+nc) -- staged through shared memory, then one contiguous coalesced copy.
-template <int LAYOUT>
+// quarter of the classes (same decomposition as the loss kernel); per-channel float4 stores.
 __global__ void __launch_bounds__(kDecThreads) k_decode_infer(LevelSet L, int nc, float *__restrict__ out) {
-    extern __shared__ float s_out[];           // LAYOUT 1: [kChunk][R] staging
     __shared__ float s_d[4][kChunk];
     const int b = blockIdx.y, chunk = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -62,16 +59,9 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer(LevelSet L, int nc
             o[2][k] = (x2 - x1) * st;
             o[3][k] = (y2 - y1) * st;
         }
-        if (LAYOUT == 0) {
 #pragma unroll
-            for (int c = 0; c < 4; ++c)
-                *reinterpret_cast<float4 *>(out + ((size_t)b * R + c) * A + a0) = make_float4(o[c][0], o[c][1], o[c][2], o[c][3]);
-        } else {
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-#pragma unroll
-                for (int c = 0; c < 4; ++c) s_out[(size_t)(lane * 4 + k) * R + c] = o[c][k];
-        }
+        for (int c = 0; c < 4; ++c)
+            *reinterpret_cast<float4 *>(out + ((size_t)b * R + c) * A + a0) = make_float4(o[c][0], o[c][1], o[c][2], o[c][3]);
     }
     if (live) {
         const int per = (nc + 3) >> 2;
@@ -81,27 +71,7 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer(LevelSet L, int nc
         for (int c = c_lo; c < c_hi; ++c) {
             const float4 xv = __ldg(reinterpret_cast<const float4 *>(xc + (size_t)c * hw));
             const float4 s = make_float4(sigmoid_fast(xv.x), sigmoid_fast(xv.y), sigmoid_fast(xv.z), sigmoid_fast(xv.w));
-            if (LAYOUT == 0) {
-                *reinterpret_cast<float4 *>(out + ((size_t)b * R + 4 + c) * A + a0) = s;
-            } else {
-                s_out[(size_t)(lane * 4 + 0) * R + 4 + c] = s.x;
-                s_out[(size_t)(lane * 4 + 1) * R + 4 + c] = s.y;
-                s_out[(size_t)(lane * 4 + 2) * R + 4 + c] = s.z;
-                s_out[(size_t)(lane * 4 + 3) * R + 4 + c] = s.w;
-            }
-        }
-    }
-    if (LAYOUT == 1) {
-        __syncthreads();
-        const int rows = min(kChunk, hw - c0);
-        float *dst = out + ((size_t)b * A + L.a_off[l] + c0) * R;
-        const int total = rows * R;
-        if (((total | R) & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {      // the block's rows are one aligned run
-            const float4 *s4 = reinterpret_cast<const float4 *>(s_out);
-            float4 *d4 = reinterpret_cast<float4 *>(dst);
-            for (int i = tid; i < (total >> 2); i += kDecThreads) d4[i] = s4[i];
-        } else {
-            for (int i = tid; i < total; i += kDecThreads) dst[i] = s_out[i];
+            *reinterpret_cast<float4 *>(out + ((size_t)b * R + 4 + c) * A + a0) = s;
         }
     }
 }
@@ -109,9 +79,7 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer(LevelSet L, int nc
 // The same decode for head shapes the vector kernel cannot take (a level with h*w % 4 != 0, or pointers that are not
 // 16-byte aligned -- the reference accepts any image size, models/yolo11_modules.py:248-266): thread = one anchor, every
 // load and store of a warp is a contiguous run of 4-byte elements.  Block = 128 consecutive anchors of one level.
-template <int LAYOUT>
 __global__ void __launch_bounds__(kDecThreads) k_decode_infer_any(LevelSet L, int nc, float *__restrict__ out) {
-    extern __shared__ float s_out[];           // LAYOUT 1: [kChunk][R] staging
     const int b = blockIdx.y, chunk = blockIdx.x;
     const int tid = threadIdx.x;
     int l = 0;
@@ -139,30 +107,111 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer_any(LevelSet L, in
         }
         const int iy = i / w, ix = i - iy * w;
         const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
-        const float x1 = gx - dm[0], y1 = gy - dm[1], x2 = gx + dm[2], y2 = gy + dm[3];
+        // explicit roundings: dm = d * inv_s must not be contracted into these (the other two decode kernels pass it
+        // through shared memory; the three agree bit for bit)
+        const float x1 = YS_SUB(gx, dm[0]), y1 = YS_SUB(gy, dm[1]), x2 = YS_ADD(gx, dm[2]), y2 = YS_ADD(gy, dm[3]);
         float o[4];
         o[0] = (x1 + x2) / 2 * st;      // dist2bbox(xywh=True) * strides  (models/yolo11_modules.py:263, :309-311)
         o[1] = (y1 + y2) / 2 * st;
         o[2] = (x2 - x1) * st;
         o[3] = (y2 - y1) * st;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            if (LAYOUT == 0) out[((size_t)b * R + c) * A + a] = o[c];
-            else s_out[(size_t)tid * R + c] = o[c];
-        }
+        for (int c = 0; c < 4; ++c) out[((size_t)b * R + c) * A + a] = o[c];
         const float *xc = xin + (size_t)64 * hw;
-        for (int c = 0; c < nc; ++c) {
-            const float sg = sigmoid_fast(__ldg(xc + (size_t)c * hw));
-            if (LAYOUT == 0) out[((size_t)b * R + 4 + c) * A + a] = sg;
-            else s_out[(size_t)tid * R + 4 + c] = sg;
+        for (int c = 0; c < nc; ++c) out[((size_t)b * R + 4 + c) * A + a] = sigmoid_fast(__ldg(xc + (size_t)c * hw));
+    }
+}
+
+// Anchor-major output (B, A, 4+nc) for ANY head shape -- the layout decode_predictions_for_metrics consumes
+// (train_yolo11_cuda.py:289-301).  Block = 128 consecutive anchors of one level; lane = anchors lane + 32 k (k = 0..3), so
+// every global load of a warp is one coalesced 128-byte row piece and no input alignment is needed.  The block's rows
+// are staged in shared memory with row pitch P and leave as one contiguous run:
+//   VEC  (P = R, R % 8 == 4, e.g. nc = 80): a lane holds four channels of one anchor and stores them as one 16-byte
+//        word; within a quarter warp the words of consecutive anchors fall in distinct 16-byte bank groups (R / 4 is
+//        odd), and the copy-out is a flat float4 copy.
+//   !VEC (P odd): scalar stores, conflict-free because P is odd; scalar, fully coalesced copy-out.
+// (r01/r02's version kept thread = 4 consecutive anchors: a 16-way bank conflict on every staging store, 0.58 of peak.)
+template <bool VEC>
+__global__ void __launch_bounds__(kDecThreads) k_decode_infer_am(LevelSet L, int nc, int P, float *__restrict__ out) {
+    extern __shared__ __align__(16) float s_out[];           // [kChunk][P] staging
+    __shared__ float s_d[4][kChunk];
+    const int b = blockIdx.y, chunk = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int l = 0;
+#pragma unroll
+    for (int k = 1; k < YS_MAX_LEVELS; ++k)
+        if (k < L.n && chunk >= L.chunk_off[k]) l = k;
+    const int hw = L.hw[l], w = L.w[l];
+    const float st = L.stride[l];
+    const int c0 = (chunk - L.chunk_off[l]) * kChunk;
+    const int rows = min(kChunk, hw - c0);
+    const int R = 4 + nc;
+    const float *xin = L.x[l] + (size_t)b * L.C * hw + c0;
+
+    // box side `warp` of the block's 128 anchors
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int r = lane + 32 * k;
+        float z[16];
+        const float *xs = xin + (size_t)(warp * 16) * hw + (r < rows ? r : 0);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) z[j] = __ldg(xs + (size_t)j * hw);
+        float m2, inv_s;
+        s_d[warp][r] = dfl_stats16(z, m2, inv_s);
+    }
+    // classes: warp takes the groups of four channels g = warp, warp + 4, ...
+    const float *xc = xin + (size_t)64 * hw;
+    for (int c = warp * 4; c < nc; c += 16) {
+        float v[4][4];    // [k][channel]
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int r = lane + 32 * k;
+            const float *xr = xc + (r < rows ? r : 0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[k][j] = (VEC || c + j < nc) ? __ldg(xr + (size_t)(c + j) * hw) : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float *dst = s_out + (size_t)(lane + 32 * k) * P + 4 + c;
+            if (VEC) {
+                *reinterpret_cast<float4 *>(dst) = make_float4(sigmoid_fast(v[k][0]), sigmoid_fast(v[k][1]),
+                                                                sigmoid_fast(v[k][2]), sigmoid_fast(v[k][3]));
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (c + j < nc) dst[j] = sigmoid_fast(v[k][j]);
+            }
         }
     }
-    if (LAYOUT == 1) {
-        __syncthreads();
-        const int rows = min(kChunk, hw - c0);
-        float *dst = out + ((size_t)b * A + L.a_true_off[l] + c0) * R;
-        const int total = rows * R;
-        for (int k = tid; k < total; k += kDecThreads) dst[k] = s_out[k];
+    __syncthreads();
+    {   // box rows: thread = one anchor
+        const int r = tid, i = c0 + r;
+        const int iy = i / w, ix = i - iy * w;
+        const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
+        const float x1 = gx - s_d[0][r], y1 = gy - s_d[1][r];
+        const float x2 = gx + s_d[2][r], y2 = gy + s_d[3][r];
+        // dist2bbox(xywh=True) * strides  (models/yolo11_modules.py:263, :309-311)
+        const float4 o = make_float4((x1 + x2) / 2 * st, (y1 + y2) / 2 * st, (x2 - x1) * st, (y2 - y1) * st);
+        float *dst = s_out + (size_t)r * P;
+        if (VEC) *reinterpret_cast<float4 *>(dst) = o;
+        else { dst[0] = o.x; dst[1] = o.y; dst[2] = o.z; dst[3] = o.w; }
+    }
+    __syncthreads();
+    float *dst = out + ((size_t)b * L.A_true + L.a_true_off[l] + c0) * R;
+    const int total = rows * R;
+    if (VEC) {
+        const float4 *s4 = reinterpret_cast<const float4 *>(s_out);
+        float4 *d4 = reinterpret_cast<float4 *>(dst);
+#pragma unroll 4
+        for (int i = tid; i < (total >> 2); i += kDecThreads) d4[i] = s4[i];
+    } else {
+        int row = tid / R, col = tid - row * R;            // kDecThreads = q R + rem: advance (row, col) without dividing
+        const int q = kDecThreads / R, rem = kDecThreads - q * R;
+        for (int i = tid; i < total; i += kDecThreads) {
+            dst[i] = s_out[(size_t)row * P + col];
+            row += q; col += rem;
+            if (col >= R) { col -= R; ++row; }
+        }
     }
 }
 
@@ -279,20 +328,22 @@ extern "C" int ys_decode_infer(int n_levels, const float *const *level_x_host, c
     int rc = build_levels_dec(L, n_levels, level_x_host, level_h_host, level_w_host, level_stride_host, nc, reg_max, all_vec);
     if (rc) return rc;
     dim3 grid(L.n_chunks, B);
-    const size_t smem = layout == 1 ? (size_t)kChunk * (4 + nc) * sizeof(float) : 0;
-    YS_REQUIRE(smem <= 200 * 1024, YS_ERR_UNSUPPORTED, "nc too large for the staged layout (%d)", nc);
-    // float4 kernel when every level's rows (and, for the channels-first output, every output row) are 16-byte aligned
-    const bool vec = all_vec && (layout == 1 || L.A % 4 == 0);
     if (layout == 0) {
-        if (vec) k_decode_infer<0><<<grid, kDecThreads, 0, stream>>>(L, nc, out);
-        else k_decode_infer_any<0><<<grid, kDecThreads, 0, stream>>>(L, nc, out);
+        // float4 kernel when every level's rows and every output row are 16-byte aligned
+        if (all_vec && L.A % 4 == 0) k_decode_infer<<<grid, kDecThreads, 0, stream>>>(L, nc, out);
+        else k_decode_infer_any<<<grid, kDecThreads, 0, stream>>>(L, nc, out);
     } else {
+        const int R = 4 + nc;
+        const bool vec = (R & 7) == 4;                 // rows of R floats: 16-byte words, R / 4 odd
+        const int P = vec ? R : (R | 1);
+        const size_t smem = (size_t)kChunk * P * sizeof(float);
+        YS_REQUIRE(smem <= 200 * 1024, YS_ERR_UNSUPPORTED, "nc too large for the staged layout (%d)", nc);
         static DeviceOnce once_dec[2];
-        rc = optin_smem(vec ? (const void *)k_decode_infer<1> : (const void *)k_decode_infer_any<1>, 200 * 1024, once_dec[vec ? 0 : 1],
-                        "k_decode_infer");
+        rc = optin_smem(vec ? (const void *)k_decode_infer_am<true> : (const void *)k_decode_infer_am<false>, 200 * 1024,
+                        once_dec[vec ? 0 : 1], "k_decode_infer_am");
         if (rc) return rc;
-        if (vec) k_decode_infer<1><<<grid, kDecThreads, smem, stream>>>(L, nc, out);
-        else k_decode_infer_any<1><<<grid, kDecThreads, smem, stream>>>(L, nc, out);
+        if (vec) k_decode_infer_am<true><<<grid, kDecThreads, smem, stream>>>(L, nc, P, out);
+        else k_decode_infer_am<false><<<grid, kDecThreads, smem, stream>>>(L, nc, P, out);
     }
     YS_CHECK_LAUNCH("k_decode_infer");
     return YS_OK;

@@ -36,19 +36,18 @@ __device__ __forceinline__ int centres_inside(float lo, float hi, int n, float s
     return max(0, i1 - i0 + 1);
 }
 
-__global__ void __launch_bounds__(kPackThreads)
-k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *__restrict__ cls, const float4 *__restrict__ bboxes,
-          int N, int B, int nc, float sx, float sy, int *__restrict__ gt_off, int *__restrict__ rank,
-          int *__restrict__ cursor_g, float4 *__restrict__ gt_box, int *__restrict__ gt_label,
-          unsigned char *__restrict__ risk, unsigned long long *__restrict__ best_key, int *__restrict__ owned_cnt,
-          int *__restrict__ gt_flags, unsigned *__restrict__ counters, int n_counters, int *__restrict__ img_order,
-          int n_identity) {
-    __shared__ int s_cursor[kPackSmemB];
-    __shared__ int s_weight[kOrderMaxB];
-    __shared__ int s_part[kPackThreads / 32];
-    __shared__ int s_unsorted;
+// The general packing, one block of kPackThreads threads: any row order, rows with an image id outside [0, B) ignored,
+// any N and B.  Shared arrays are the caller's (s_cursor[kPackSmemB], s_weight[kOrderMaxB], s_part[32], s_unsorted[1]).
+__device__ void pack_gt_general(const LevelSet &L, const long long *__restrict__ batch_idx, const long long *__restrict__ cls,
+                                const float4 *__restrict__ bboxes, int N, int B, int nc, float sx, float sy,
+                                int *__restrict__ gt_off, int *__restrict__ rank, int *__restrict__ cursor_g,
+                                float4 *__restrict__ gt_box, int *__restrict__ gt_label, unsigned char *__restrict__ risk,
+                                unsigned long long *__restrict__ best_key, int *__restrict__ owned_cnt,
+                                int *__restrict__ gt_flags, unsigned *__restrict__ counters, int n_counters,
+                                int *__restrict__ img_order, int n_identity, int *s_cursor, int *s_weight, int *s_part,
+                                int *s_unsorted_p) {
+    int &s_unsorted = *s_unsorted_p;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    cudaTriggerProgrammaticLaunchCompletion();      // k_assign may start its prologue (it waits for this grid to finish)
     volatile int *cursor = (B <= kPackSmemB) ? (volatile int *)s_cursor : (volatile int *)cursor_g;
     for (int i = tid; i < B; i += kPackThreads) cursor[i] = 0;
     for (int i = tid; i < n_counters; i += kPackThreads) counters[i] = 0u;    // arrival counters of k_assign / k_loss
@@ -198,6 +197,134 @@ k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *
             r = n_identity;
             for (int o = n_identity; o < B; ++o) {
                 const int wo = s_weight[o];
+                r += (wo > wb || (wo == wb && o < b)) ? 1 : 0;
+            }
+        }
+        img_order[r] = b;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// GT packing above 1024 GT or 1024 images (the dense 1280 px scene of BASELINE configs[4]: 19200 GT per batch).
+// Multi-block, one row per thread.  What the reference collate produces -- rows sorted by image, every id valid
+// (datasets/crater_dataset_cuda.py:327-341) -- needs no coordination between blocks: the packed position of row i is i,
+// gt_off[b] is the first row of image b (written by the thread that sees the boundary), the hints come from the
+// row's own box and from its image's other rows, which lie within 64 rows of it whenever the containment hint applies
+// (read from a halo'd shared-memory copy).  Every block checks its rows' order; the last block to finish (arrival
+// counter, reset by that block) either ranks the images for k_assign's launch order or, if any block saw a row out of
+// order or an invalid id, redoes the whole packing with pack_gt_general (one block; r02's single-block kernel took 70 us
+// of the 1.03 ms configs[4] step this way).  Same outputs as pack_gt_general, bit for bit.  pack_ctr = {arrivals, redo
+// flag, launch weight of image 0, 1, ...}: zeroed by a memset node in front of this kernel.
+// ---------------------------------------------------------------------------------------------------
+constexpr int kPackHalo = kContainMaxGt;                       // rows of the neighbouring blocks each block also loads
+constexpr int kPackRaw = (kPackSmemB + kOrderMaxB + 32 + 4) * 4;   // bytes: the general path's arrays (>= the sorted path's)
+static_assert((kPackThreads + 2 * kPackHalo) * (4 + 16) <= kPackRaw, "sorted-path staging must fit the shared buffer");
+
+__global__ void __launch_bounds__(kPackThreads)
+k_pack_gt(LevelSet L, const long long *__restrict__ batch_idx, const long long *__restrict__ cls, const float4 *__restrict__ bboxes,
+          int N, int B, int nc, float sx, float sy, int *__restrict__ gt_off, int *__restrict__ rank,
+          int *__restrict__ cursor_g, float4 *__restrict__ gt_box, int *__restrict__ gt_label,
+          unsigned char *__restrict__ risk, unsigned long long *__restrict__ best_key, int *__restrict__ owned_cnt,
+          int *__restrict__ gt_flags, unsigned *__restrict__ counters, int n_counters, int *__restrict__ img_order,
+          int n_identity, unsigned *__restrict__ pack_ctr) {
+    int *weight_g = reinterpret_cast<int *>(pack_ctr + 2);
+    __shared__ __align__(16) unsigned char s_raw[kPackRaw];
+    __shared__ int s_last;
+    const int tid = threadIdx.x;
+    cudaTriggerProgrammaticLaunchCompletion();      // k_assign may start its prologue (it waits for this grid to finish)
+    // ---- sorted-input pass: rows [row0 - halo, row0 + 1024 + halo) staged in shared memory
+    float4 *s_box = reinterpret_cast<float4 *>(s_raw);                              // [1024 + 2 halo]
+    int *s_id = reinterpret_cast<int *>(s_raw + (kPackThreads + 2 * kPackHalo) * 16);   // [1024 + 2 halo], -1 outside [0, N)
+    const int row0 = blockIdx.x * kPackThreads;
+    const bool order_images = B <= kOrderMaxB;
+    for (int k = tid; k < kPackThreads + 2 * kPackHalo; k += kPackThreads) {
+        const int r = row0 - kPackHalo + k;
+        int id = -1;
+        float4 qp = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r >= 0 && r < N) {
+            const long long id64 = batch_idx[r];
+            id = (id64 >= 0 && id64 < B) ? (int)id64 : -2;
+            const float4 q = bboxes[r];
+            qp = make_float4(YS_MUL(q.x, sx), YS_MUL(q.y, sy), YS_MUL(q.z, sx), YS_MUL(q.w, sy));   // (losses/yolo_v8_loss.py:515-516)
+        }
+        s_id[k] = id;
+        s_box[k] = qp;
+    }
+    __syncthreads();
+    const int i = row0 + tid, k = tid + kPackHalo;
+    if (i < N) {
+        const int id = s_id[k];
+        const int prev = i > 0 ? s_id[k - 1] : -1;             // image of row i-1 (-1: there is none, -2: invalid id)
+        const bool bad = id < 0 || (i > 0 && (prev < 0 || prev > id));
+        if (bad) {
+            pack_ctr[1] = 1u;                                  // someone has to redo this properly
+        } else {
+            for (int j = prev + 1; j <= id; ++j) gt_off[j] = i;        // images prev+1 .. id start at row i
+            if (i == N - 1)
+                for (int j = id + 1; j <= B; ++j) gt_off[j] = N;
+            best_key[i] = 0xFFFFFFFFull;      // = argmax_key(IoU 0, anchor 0): the first maximum of an all-zero column
+            owned_cnt[i] = 0;
+            gt_flags[i] = 0;
+            const float4 qp = s_box[k];
+            gt_box[i] = qp;
+            long long c = cls[i];
+            c = c < 0 ? 0 : (c > nc - 1 ? nc - 1 : c);
+            gt_label[i] = (int)c;
+            int centres = 0;
+            for (int l = 0; l < L.n && centres <= kRiskMaxCentres; ++l)
+                centres += centres_inside(qp.x, qp.z, L.w[l], L.stride[l]) * centres_inside(qp.y, qp.w, (int)((float)L.hw[l] * __frcp_rn((float)L.w[l]) + 0.5f), L.stride[l]);
+            int rk = centres <= kRiskMaxCentres ? 1 : 0;
+            int wgt = (centres <= kRiskMaxCentres ? (centres <= 4 ? 64 : 1) : 0) * 2048 + 1;
+            if (!rk) {
+                // containment hint (images with at most kContainMaxGt GT): the image's rows are within the halo
+                int lo = k, hi = k + 1;
+                while (lo > k - kPackHalo && s_id[lo - 1] == id) --lo;
+                while (hi < k + kPackHalo + 1 && s_id[hi] == id) ++hi;
+                if (hi - lo <= kContainMaxGt) {            // more rows than that: one of the two walks ran its full length
+                    bool inside = false;
+                    for (int m = lo; m < hi; ++m) {
+                        const float4 o = s_box[m];
+                        inside |= (m != k) && o.x <= qp.x && o.y <= qp.y && o.z >= qp.z && o.w >= qp.w;
+                    }
+                    if (inside) { rk = 1; wgt += 2048; }
+                }
+            }
+            risk[i] = (unsigned char)rk;
+            if (order_images) atomicAdd(&weight_g[id], wgt);
+        }
+    }
+    if (N == 0 && blockIdx.x == 0)
+        for (int j = tid; j <= B; j += kPackThreads) gt_off[j] = 0;
+    // ---- arrival; the last block finishes the job
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = (atomicAdd(&pack_ctr[0], 1u) == gridDim.x - 1) ? 1 : 0;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const bool redo = *reinterpret_cast<volatile unsigned *>(&pack_ctr[1]) != 0u;
+    int *s_w = reinterpret_cast<int *>(s_raw);
+    if (!redo && order_images)
+        for (int b = tid; b < B; b += kPackThreads) s_w[b] = __ldcg(&weight_g[b]);
+    __syncthreads();
+    if (redo) {
+        int *s_cursor = reinterpret_cast<int *>(s_raw);
+        int *s_weight = s_cursor + kPackSmemB;
+        int *s_part = s_weight + kOrderMaxB;
+        pack_gt_general(L, batch_idx, cls, bboxes, N, B, nc, sx, sy, gt_off, rank, cursor_g, gt_box, gt_label, risk, best_key,
+                        owned_cnt, gt_flags, counters, n_counters, img_order, n_identity, s_cursor, s_weight, s_part,
+                        s_part + 32);
+        return;
+    }
+    for (int c = tid; c < n_counters; c += kPackThreads) counters[c] = 0u;    // arrival counters of k_assign / k_loss
+    // launch order of the images in k_assign: heaviest expected fix-up first (a scheduling hint only)
+    for (int b = tid; b < B; b += kPackThreads) {
+        int r = b;       // the first n_identity slots keep their own image (k_assign decodes those before it may read this)
+        if (order_images && b >= n_identity) {
+            const int wb = s_w[b];
+            r = n_identity;
+            for (int o = n_identity; o < B; ++o) {
+                const int wo = s_w[o];
                 r += (wo > wb || (wo == wb && o < b)) ? 1 : 0;
             }
         }
@@ -602,6 +729,7 @@ struct LossWorkspace {
     unsigned long long *best_key;
     float *norm, *tss, *scan_partial;
     double *img_sum;
+    unsigned *pack_ctr;      // k_pack_gt (multi-block): [0] blocks finished, [1] "redo in one block" flag, [2 + b] launch weight of image b
     unsigned *counters;      // [0] images finished (k_assign), [1] blocks finished (k_loss), [2 + b] blocks of image b finished
     size_t bytes;
 };
@@ -613,6 +741,7 @@ static void carve_loss(LossWorkspace &W, void *base, size_t cap, int B, int A_tr
     const size_t N = (size_t)(n_gt > 0 ? n_gt : 1);
     const size_t A = (size_t)padded_anchor_bound(A_true);
     W.counters = c.take<unsigned>((size_t)B + 2);
+    W.pack_ctr = c.take<unsigned>((size_t)B + 2);
     W.tss = c.take<float>(64);
     W.gt_off = c.take<int>((size_t)B + 1);
     W.cursor = c.take<int>((size_t)B + 1);
@@ -694,11 +823,16 @@ extern "C" int ys_detection_loss(int n_levels, const float *const *level_x_host,
                                                         (const float4 *)bboxes, n_gt, B, nc, scale_x, scale_y, W.gt_off,
                                                         W.gt_box, W.gt_label, W.risk, W.best_key, W.owned_cnt,
                                                         W.gt_flags, W.counters, B + 2, W.img_order, n_identity);
-        else
-        k_pack_gt<<<1, kPackThreads, 0, stream>>>(L, (const long long *)batch_idx, (const long long *)cls,
-                                                  (const float4 *)bboxes, n_gt, B, nc, scale_x, scale_y, W.gt_off, W.rank,
-                                                  W.cursor, W.gt_box, W.gt_label, W.risk, W.best_key, W.owned_cnt,
-                                                  W.gt_flags, W.counters, B + 2, W.img_order, n_identity);
+        else {
+            cudaError_t me = cudaMemsetAsync(W.pack_ctr, 0, ((size_t)B + 2) * sizeof(unsigned), stream);
+            YS_REQUIRE(me == cudaSuccess, (int)me, "cudaMemsetAsync(pack_ctr): %s", cudaGetErrorString(me));
+            const int blocks = n_gt > 0 ? (n_gt + kPackThreads - 1) / kPackThreads : 1;
+            k_pack_gt<<<blocks, kPackThreads, 0, stream>>>(L, (const long long *)batch_idx, (const long long *)cls,
+                                                           (const float4 *)bboxes, n_gt, B, nc, scale_x, scale_y, W.gt_off,
+                                                           W.rank, W.cursor, W.gt_box, W.gt_label, W.risk, W.best_key,
+                                                           W.owned_cnt, W.gt_flags, W.counters, B + 2, W.img_order,
+                                                           n_identity, W.pack_ctr);
+        }
         YS_CHECK_LAUNCH("k_pack_gt");
     }
 
