@@ -92,6 +92,36 @@ def test_loss_dense_scene_vs_oracle(cuda_lib, seed, B, imgsz, kw):
     spliced_case(seed, B, imgsz, kw.get("fixed_count", 20), kw)
 
 
+def test_loss_ownerless_gt_outside_the_risk_hint(cuda_lib):
+    """A GT with hundreds of anchor centres inside that is not contained in any other GT, yet owns nothing: two
+    smaller GT cover it and win every arg-max contest (the predicted boxes are made tiny, so IoU ~ 1 / GT area).
+    k_pack_gt's launch-order hint does not see such a GT; loop 2 (:146-162) fires for it all the same.  Indices bit-exact
+    against the spliced oracle, in a sparse image and next to an image with more than 64 GT."""
+    B, imgsz, nc = 3, 640, 80
+    feats = synth.make_head_levels(B, imgsz, nc, 16, seed=260)
+    for f in feats:
+        f[:, 0:64:16] += 9.0            # bin 0 of every side dominates: predicted boxes of a fraction of a cell
+    covered = torch.tensor([[100.0, 100.0, 300.0, 300.0],       # A: 625 stride-8 centres inside, not inside B1 or B2
+                            [99.0, 99.0, 301.0, 200.5],         # B1 and B2 cover A and are smaller
+                            [99.0, 199.5, 301.0, 301.0],
+                            [400.0, 50.0, 600.0, 250.0],        # a second such triple, listed cover-first
+                            [399.0, 49.0, 500.5, 251.0],
+                            [499.5, 49.0, 601.0, 251.0],
+                            [20.0, 400.0, 90.0, 470.0]]) / imgsz
+    order = torch.tensor([1, 0, 2, 4, 5, 3, 6])
+    dense = synth.make_gt_batch(1, nc, 70, seed=262, imgsz=imgsz, fixed_count=70, p_nested=0.3)
+    batch = {"batch_idx": torch.cat((torch.zeros(7, dtype=torch.long), torch.ones(7, dtype=torch.long),
+                                     torch.full((70,), 2, dtype=torch.long))),
+             "cls": torch.cat((torch.arange(7).view(7, 1), torch.arange(7).view(7, 1) + 10, dense["cls"])),
+             "bboxes": torch.cat((covered, covered[order], dense["bboxes"]))}
+    ex, parts = spliced_check(feats, batch, B, imgsz, nc)
+    # loop 2 fires for the covered GT, and the final resolve (:165) hands the forced anchor back to the smaller cover
+    tgi = ex["target_gt_idx"]
+    assert int((tgi[0] == 0).sum()) == 0 and int((tgi[0] == 3).sum()) == 0
+    assert int((tgi[1] == 1).sum()) == 0 and int((tgi[1] == 5).sum()) == 0
+    assert int((tgi[0] == 1).sum()) > 300 and int((tgi[1] == 0).sum()) > 300
+
+
 def test_loss_many_images_mixed_counts_multiblock_pack(cuda_lib):
     """More than 1024 GT spread over 64 images with 0..60 GT each (empty images in the middle and at the end): the
     multi-block k_pack_gt's sorted path -- image boundaries found per row, gaps in gt_off filled, containment hint
@@ -109,9 +139,13 @@ def test_loss_vs_oracle_other_class_counts(cuda_lib, seed, nc):
 
 
 def spliced_case(seed, B, imgsz, max_gt, kw, nc=80, shapes=None):
-    from oracle import ref_port as orc
     feats = synth.make_head_levels(B, imgsz, nc, 16, seed=seed, shapes=shapes)
     batch = synth.make_gt_batch(B, nc, max_gt, seed=seed + 1, imgsz=imgsz, **kw)
+    return spliced_check(feats, batch, B, imgsz, nc)
+
+
+def spliced_check(feats, batch, B, imgsz, nc=80):
+    from oracle import ref_port as orc
     total, items, grads, crit = run_cuda(feats, batch, nc, export=True)
     leaves = [f.clone().requires_grad_(True) for f in feats]
     rtotal, ritems, parts = orc.detection_loss(leaves, batch, nc, 16, synth.LEVEL_STRIDES, return_parts=True)
@@ -149,6 +183,7 @@ def spliced_case(seed, B, imgsz, max_gt, kw, nc=80, shapes=None):
         assert torch.allclose(items, ritems, rtol=RTOL, atol=1e-7), (items, ritems)
         assert torch.allclose(total, rtotal.detach(), rtol=RTOL)
         assert_grads_close(grads, [l.grad for l in leaves])
+    return ex, parts
 
 
 def test_loss_config2_exact_bench_inputs(cuda_lib):

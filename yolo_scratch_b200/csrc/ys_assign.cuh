@@ -540,8 +540,19 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         //     the IoU bits (>= 0, so they order as integers), lowest lane among the ties, one shared atomicMax per warp.
         //     Keys with IoU 0 are never recorded: k_pack_gt preset every key to (IoU 0, anchor 0), the first maximum
         //     of an all-zero column.
+#ifdef YS_REACH_WINDOW       // r01/r02: the a-priori window (a decoded side is at most kDflReach cells long)
         const float reach = kDflReach * L.stride[lvl];
         const float rx0 = wx_min - reach, rx1 = wx_max + reach, ry0 = wy_min - reach, ry1 = wy_max + reach;
+#else
+        // "Within reach" of this warp = intersecting the union of its 32 decoded boxes: a GT with q.x >= max p.z (or any of
+        // the three symmetric cases) has min(p.z, q.z) - max(p.x, q.x) <= 0 for every lane, and iou_assign_lazy returns
+        // exactly 0 for those -- the same floats, no slack needed.  Tighter than the a-priori bound of kDflReach cells
+        // around the centres whenever the predicted sides are shorter than 15.5 cells (always, in practice).
+        const float rx0 = ord_to_float(__reduce_min_sync(0xffffffffu, live ? float_to_ord(p.x) : 0xffffffffu));
+        const float ry0 = ord_to_float(__reduce_min_sync(0xffffffffu, live ? float_to_ord(p.y) : 0xffffffffu));
+        const float rx1 = ord_to_float(__reduce_max_sync(0xffffffffu, live ? float_to_ord(p.z) : 0u));
+        const float ry1 = ord_to_float(__reduce_max_sync(0xffffffffu, live ? float_to_ord(p.w) : 0u));
+#endif
         const bool warp_live = __any_sync(0xffffffffu, live);
         for (int t = 0; t < ntiles; ++t) {
             const int t0 = t * kGtTile;
@@ -720,11 +731,27 @@ __device__ __forceinline__ void fix_argmax(const LevelSet &L, const AssignIO &io
         const float area_q = area_eps_h(gq.x, gq.y, gq.z, gq.w);
         float best = -1.f;          // thread-local first maximum over this thread's anchors (ascending a)
         int best_a = 0;
-#pragma unroll 8
-        for (int a = tid; a < L.A; a += kScanThreads) {
-            const float4 p = FUSED ? __ldcg(pb + a) : pb[a];
-            const float ov = pair_ov<FUSED>(io, p, area_eps_h(p.x, p.y, p.z, p.w), gq, area_q);
-            if (ov > best) { best = ov; best_a = a; }
+        // fused: the per-anchor state lives in the padded anchor space and only the live entries were written.
+        // Four boxes are fetched before the first is used (the loop was one L2 round trip per anchor otherwise: 12 us
+        // for the 8400 anchors of a 640 px image, measured with -DYS_FIXTIME).
+        for (int l = 0; l < (FUSED ? L.n : 1); ++l) {
+            const int a0 = FUSED ? L.a_off[l] : 0, a1 = a0 + (FUSED ? L.hw[l] : L.A);
+            for (int ab = a0 + tid; ab < a1; ab += 4 * kScanThreads) {
+                float4 pv[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int a = ab + u * kScanThreads;
+                    pv[u] = a < a1 ? (FUSED ? __ldcg(pb + a) : pb[a]) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int a = ab + u * kScanThreads;
+                    if (a < a1) {
+                        const float ov = pair_ov<FUSED>(io, pv[u], area_eps_h(pv[u].x, pv[u].y, pv[u].z, pv[u].w), gq, area_q);
+                        if (ov > best) { best = ov; best_a = a; }
+                    }
+                }
+            }
         }
         unsigned long long key = best >= 0.f ? argmax_key(best, (unsigned)best_a) : 0ull;
         key = warp_max(key);

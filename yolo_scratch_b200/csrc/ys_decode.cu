@@ -7,6 +7,13 @@
 namespace ys {
 
 constexpr int kDecThreads = 128;
+#ifndef YS_DEC_MINB
+#define YS_DEC_MINB 5        // resident blocks per SM the anchor-major kernel is compiled for (shared memory allows 5)
+#endif
+#ifndef YS_DEC_GROUPS
+#define YS_DEC_GROUPS 1      // class groups (of four channels) a warp of the anchor-major kernel loads per trip (measured on
+                             // B200, B=64: 1 / 2 / 3 groups at 5 blocks per SM 0.104 / 0.106 / 0.105 ms; 4 blocks 0.108-0.117; 3 blocks 0.137)
+#endif
 
 // Channels-first output (B, 4+nc, A), what Detect.inference returns (models/yolo11_modules.py:263-266).
 // One block = 128 consecutive anchors of one level of one image; thread = 4 anchors; warp w = box side w and a
@@ -132,7 +139,7 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer_any(LevelSet L, in
 //   !VEC (P odd): scalar stores, conflict-free because P is odd; scalar, fully coalesced copy-out.
 // (r01/r02's version kept thread = 4 consecutive anchors: a 16-way bank conflict on every staging store, 0.58 of peak.)
 template <bool VEC>
-__global__ void __launch_bounds__(kDecThreads) k_decode_infer_am(LevelSet L, int nc, int P, float *__restrict__ out) {
+__global__ void __launch_bounds__(kDecThreads, YS_DEC_MINB) k_decode_infer_am(LevelSet L, int nc, int P, float *__restrict__ out) {
     extern __shared__ __align__(16) float s_out[];           // [kChunk][P] staging
     __shared__ float s_d[4][kChunk];
     const int b = blockIdx.y, chunk = blockIdx.x;
@@ -159,27 +166,36 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer_am(LevelSet L, int
         float m2, inv_s;
         s_d[warp][r] = dfl_stats16(z, m2, inv_s);
     }
-    // classes: warp takes the groups of four channels g = warp, warp + 4, ...
+    // classes: warp takes the groups of four channels g = warp, warp + 4, ...  The kernel is bound by load latency (ncu:
+    // long scoreboard 12 per issue); what helped was the register budget of 5 blocks per SM (loads hoisted: 0.124 ->
+    // 0.104 ms), not more groups per trip
     const float *xc = xin + (size_t)64 * hw;
-    for (int c = warp * 4; c < nc; c += 16) {
-        float v[4][4];    // [k][channel]
+    for (int c = warp * 4; c < nc; c += 16 * YS_DEC_GROUPS) {
+        float v[YS_DEC_GROUPS][4][4];    // [group][k][channel]
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int r = lane + 32 * k;
-            const float *xr = xc + (r < rows ? r : 0);
+        for (int g = 0; g < YS_DEC_GROUPS; ++g)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[k][j] = (VEC || c + j < nc) ? __ldg(xr + (size_t)(c + j) * hw) : 0.f;
-        }
+            for (int k = 0; k < 4; ++k) {
+                const int r = lane + 32 * k, cg = c + 16 * g;
+                const float *xr = xc + (r < rows ? r : 0);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            float *dst = s_out + (size_t)(lane + 32 * k) * P + 4 + c;
-            if (VEC) {
-                *reinterpret_cast<float4 *>(dst) = make_float4(sigmoid_fast(v[k][0]), sigmoid_fast(v[k][1]),
-                                                                sigmoid_fast(v[k][2]), sigmoid_fast(v[k][3]));
-            } else {
+                for (int j = 0; j < 4; ++j) v[g][k][j] = (cg + j < nc) ? __ldg(xr + (size_t)(cg + j) * hw) : 0.f;
+            }
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (c + j < nc) dst[j] = sigmoid_fast(v[k][j]);
+        for (int g = 0; g < YS_DEC_GROUPS; ++g) {
+            const int cg = c + 16 * g;
+            if (cg >= nc) break;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float *dst = s_out + (size_t)(lane + 32 * k) * P + 4 + cg;
+                if (VEC) {
+                    *reinterpret_cast<float4 *>(dst) = make_float4(sigmoid_fast(v[g][k][0]), sigmoid_fast(v[g][k][1]),
+                                                                    sigmoid_fast(v[g][k][2]), sigmoid_fast(v[g][k][3]));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (cg + j < nc) dst[j] = sigmoid_fast(v[g][k][j]);
+                }
             }
         }
     }
