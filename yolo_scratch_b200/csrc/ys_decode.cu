@@ -7,13 +7,6 @@
 namespace ys {
 
 constexpr int kDecThreads = 128;
-#ifndef YS_DEC_MINB
-#define YS_DEC_MINB 5        // resident blocks per SM the anchor-major kernel is compiled for (shared memory allows 5)
-#endif
-#ifndef YS_DEC_GROUPS
-#define YS_DEC_GROUPS 1      // class groups (of four channels) a warp of the anchor-major kernel loads per trip (measured on
-                             // B200, B=64: 1 / 2 / 3 groups at 5 blocks per SM 0.104 / 0.106 / 0.105 ms; 4 blocks 0.108-0.117; 3 blocks 0.137)
-#endif
 
 // Channels-first output (B, 4+nc, A), what Detect.inference returns (models/yolo11_modules.py:263-266).
 // One block = 128 consecutive anchors of one level of one image; thread = 4 anchors; warp w = box side w and a
@@ -130,19 +123,23 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer_any(LevelSet L, in
 }
 
 // Anchor-major output (B, A, 4+nc) for ANY head shape -- the layout decode_predictions_for_metrics consumes
-// (train_yolo11_cuda.py:289-301).  Block = 128 consecutive anchors of one level; lane = anchors lane + 32 k (k = 0..3), so
-// every global load of a warp is one coalesced 128-byte row piece and no input alignment is needed.  The block's rows
-// are staged in shared memory with row pitch P and leave as one contiguous run:
-//   VEC  (P = R, R % 8 == 4, e.g. nc = 80): a lane holds four channels of one anchor and stores them as one 16-byte
-//        word; within a quarter warp the words of consecutive anchors fall in distinct 16-byte bank groups (R / 4 is
-//        odd), and the copy-out is a flat float4 copy.
-//   !VEC (P odd): scalar stores, conflict-free because P is odd; scalar, fully coalesced copy-out.
-// (r01/r02's version kept thread = 4 consecutive anchors: a 16-way bank conflict on every staging store, 0.58 of peak.)
+// (train_yolo11_cuda.py:289-301).  Block = 64 consecutive anchors of one level (half a 128-anchor chunk).
+//   1. The block's whole input tile, [4*16 + nc channel rows][64 anchors], comes into shared memory by cp.async --
+//      16-byte copies when the level's rows are 16-byte aligned, 4-byte copies otherwise -- so no register holds a load
+//      and every byte of the tile is in flight at once; three blocks per SM keep ~110 KB in flight per SM.  (The
+//      register-fed version before this one was bound by load latency: long scoreboard 12 per issue, 0.73 of the HBM
+//      peak at 96 registers, 0.61 at 66.)
+//   2. Decode out of shared memory, lane = anchor (conflict-free reads of a channel row), results staged as rows of
+//      P floats:  VEC (P = R, R % 8 == 4, e.g. nc = 80): four channels of one anchor are one 16-byte word, and within a
+//      quarter warp the words of consecutive anchors fall in distinct 16-byte bank groups (R / 4 is odd);
+//      !VEC (P odd): scalar stores, conflict-free because P is odd.
+//   3. The staged rows leave as one contiguous run (float4 when VEC).
+constexpr int kAmCols = 64;
 template <bool VEC>
-__global__ void __launch_bounds__(kDecThreads, YS_DEC_MINB) k_decode_infer_am(LevelSet L, int nc, int P, float *__restrict__ out) {
-    extern __shared__ __align__(16) float s_out[];           // [kChunk][P] staging
-    __shared__ float s_d[4][kChunk];
-    const int b = blockIdx.y, chunk = blockIdx.x;
+__global__ void __launch_bounds__(kDecThreads) k_decode_infer_am(LevelSet L, int nc, int P, float *__restrict__ out) {
+    extern __shared__ __align__(16) float s_dyn_dec[];
+    __shared__ float s_d[4][kAmCols];
+    const int b = blockIdx.y, chunk = blockIdx.x >> 1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int l = 0;
 #pragma unroll
@@ -150,57 +147,65 @@ __global__ void __launch_bounds__(kDecThreads, YS_DEC_MINB) k_decode_infer_am(Le
         if (k < L.n && chunk >= L.chunk_off[k]) l = k;
     const int hw = L.hw[l], w = L.w[l];
     const float st = L.stride[l];
-    const int c0 = (chunk - L.chunk_off[l]) * kChunk;
-    const int rows = min(kChunk, hw - c0);
-    const int R = 4 + nc;
+    const int c0 = (chunk - L.chunk_off[l]) * kChunk + (blockIdx.x & 1) * kAmCols;
+    const int rows = min(kAmCols, hw - c0);
+    if (rows <= 0) return;                           // second half of a chunk that ends in its first half
+    const int R = 4 + nc, C = 64 + nc;
+    float *tile = s_dyn_dec;                         // [C][kAmCols]
+    float *s_out = s_dyn_dec + (size_t)C * kAmCols;  // [kAmCols][P]
     const float *xin = L.x[l] + (size_t)b * L.C * hw + c0;
 
-    // box side `warp` of the block's 128 anchors
+    // ---- 1. input tile -> shared memory
+    if (L.tma[l]) {                                  // rows 16-byte aligned (h*w % 4 == 0 and aligned base): c0 % 64 == 0
+        const int n16 = (rows + 3) >> 2;             // hw % 4 == 0, so a 16-byte piece never crosses the row's end
+        for (int i = tid; i < C * 16; i += kDecThreads) {
+            const int r = i >> 4, q = i & 15;
+            if (q < n16) {
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(tile + r * kAmCols + q * 4);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(xin + (size_t)r * hw + q * 4) : "memory");
+            }
+        }
+    } else {
+        for (int i = tid; i < C * kAmCols; i += kDecThreads) {
+            const int r = i >> 6, q = i & 63;
+            if (q < rows) {
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(tile + r * kAmCols + q);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(xin + (size_t)r * hw + q) : "memory");
+            }
+        }
+    }
+    asm volatile("cp.async.commit_group;\n cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+
+    // ---- 2a. box side `warp` of the 64 anchors (columns past `rows` hold stale shared memory: computed, never copied out)
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < 2; ++k) {
         const int r = lane + 32 * k;
         float z[16];
-        const float *xs = xin + (size_t)(warp * 16) * hw + (r < rows ? r : 0);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) z[j] = __ldg(xs + (size_t)j * hw);
+        for (int j = 0; j < 16; ++j) z[j] = tile[(warp * 16 + j) * kAmCols + r];
         float m2, inv_s;
         s_d[warp][r] = dfl_stats16(z, m2, inv_s);
     }
-    // classes: warp takes the groups of four channels g = warp, warp + 4, ...  The kernel is bound by load latency (ncu:
-    // long scoreboard 12 per issue); what helped was the register budget of 5 blocks per SM (loads hoisted: 0.124 ->
-    // 0.104 ms), not more groups per trip
-    const float *xc = xin + (size_t)64 * hw;
-    for (int c = warp * 4; c < nc; c += 16 * YS_DEC_GROUPS) {
-        float v[YS_DEC_GROUPS][4][4];    // [group][k][channel]
+    // ---- 2b. classes: a warp takes the groups of four channels g = warp, warp + 4, ...
+    for (int c = warp * 4; c < nc; c += 16) {
 #pragma unroll
-        for (int g = 0; g < YS_DEC_GROUPS; ++g)
+        for (int k = 0; k < 2; ++k) {
+            const int r = lane + 32 * k;
+            const float *tc = tile + (size_t)(64 + c) * kAmCols + r;
+            float *dst = s_out + (size_t)r * P + 4 + c;
+            if (VEC) {
+                *reinterpret_cast<float4 *>(dst) = make_float4(sigmoid_fast(tc[0]), sigmoid_fast(tc[kAmCols]),
+                                                                sigmoid_fast(tc[2 * kAmCols]), sigmoid_fast(tc[3 * kAmCols]));
+            } else {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int r = lane + 32 * k, cg = c + 16 * g;
-                const float *xr = xc + (r < rows ? r : 0);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) v[g][k][j] = (cg + j < nc) ? __ldg(xr + (size_t)(cg + j) * hw) : 0.f;
-            }
-#pragma unroll
-        for (int g = 0; g < YS_DEC_GROUPS; ++g) {
-            const int cg = c + 16 * g;
-            if (cg >= nc) break;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                float *dst = s_out + (size_t)(lane + 32 * k) * P + 4 + cg;
-                if (VEC) {
-                    *reinterpret_cast<float4 *>(dst) = make_float4(sigmoid_fast(v[g][k][0]), sigmoid_fast(v[g][k][1]),
-                                                                    sigmoid_fast(v[g][k][2]), sigmoid_fast(v[g][k][3]));
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        if (cg + j < nc) dst[j] = sigmoid_fast(v[g][k][j]);
-                }
+                for (int j = 0; j < 4; ++j)
+                    if (c + j < nc) dst[j] = sigmoid_fast(tc[j * kAmCols]);
             }
         }
     }
     __syncthreads();
-    {   // box rows: thread = one anchor
+    if (tid < kAmCols) {   // box rows: thread = one anchor
         const int r = tid, i = c0 + r;
         const int iy = i / w, ix = i - iy * w;
         const float gx = (float)ix + 0.5f, gy = (float)iy + 0.5f;
@@ -213,6 +218,7 @@ __global__ void __launch_bounds__(kDecThreads, YS_DEC_MINB) k_decode_infer_am(Le
         else { dst[0] = o.x; dst[1] = o.y; dst[2] = o.z; dst[3] = o.w; }
     }
     __syncthreads();
+    // ---- 3. copy-out
     float *dst = out + ((size_t)b * L.A_true + L.a_true_off[l] + c0) * R;
     const int total = rows * R;
     if (VEC) {
@@ -352,14 +358,15 @@ extern "C" int ys_decode_infer(int n_levels, const float *const *level_x_host, c
         const int R = 4 + nc;
         const bool vec = (R & 7) == 4;                 // rows of R floats: 16-byte words, R / 4 odd
         const int P = vec ? R : (R | 1);
-        const size_t smem = (size_t)kChunk * P * sizeof(float);
+        const size_t smem = ((size_t)(64 + nc) * kAmCols + (size_t)kAmCols * P) * sizeof(float);
         YS_REQUIRE(smem <= 200 * 1024, YS_ERR_UNSUPPORTED, "nc too large for the staged layout (%d)", nc);
         static DeviceOnce once_dec[2];
         rc = optin_smem(vec ? (const void *)k_decode_infer_am<true> : (const void *)k_decode_infer_am<false>, 200 * 1024,
                         once_dec[vec ? 0 : 1], "k_decode_infer_am");
         if (rc) return rc;
-        if (vec) k_decode_infer_am<true><<<grid, kDecThreads, smem, stream>>>(L, nc, P, out);
-        else k_decode_infer_am<false><<<grid, kDecThreads, smem, stream>>>(L, nc, P, out);
+        dim3 grid_am(2 * L.n_chunks, B);
+        if (vec) k_decode_infer_am<true><<<grid_am, kDecThreads, smem, stream>>>(L, nc, P, out);
+        else k_decode_infer_am<false><<<grid_am, kDecThreads, smem, stream>>>(L, nc, P, out);
     }
     YS_CHECK_LAUNCH("k_decode_infer");
     return YS_OK;
