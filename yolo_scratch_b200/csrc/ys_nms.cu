@@ -143,7 +143,8 @@ __global__ void k_nms_keys_single(const float *__restrict__ scores, int N, unsig
 // larger keys there) and is gathered straight to its place in the sorted outputs: 8192 + 256 slots instead of 16384
 // at n = 8400.
 // ---------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void nms_bitonic_desc(unsigned long long *s, int P) {      // whole block; ends on a barrier
+// Plain network, one compare-exchange per thread and step, a block barrier per step: runs shorter than 128 keys only.
+__device__ __forceinline__ void nms_bitonic_small(unsigned long long *s, int P) {      // whole block; ends on a barrier
     for (int k = 2; k <= P; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
             for (int t = threadIdx.x; t < (P >> 1); t += kSortThreads) {
@@ -159,7 +160,98 @@ __device__ __forceinline__ void nms_bitonic_desc(unsigned long long *s, int P) {
     }
 }
 
-__global__ void __launch_bounds__(kSortThreads)
+// The same network for P >= 128 with the keys in REGISTERS between steps (the plain version moves every key through
+// shared memory once per step -- 91 steps for 8192 keys: 221 us for 256 images; this one 160 us, bound by the 64-bit
+// compare / select instructions).  Two kinds of passes, each one load and one store of the run:
+//   chunk pass  a warp owns 128 consecutive slots, lane holds slots lane + 32 m (m = 0..3): the steps with distance 64
+//               and 32 are compare-exchanges inside the thread, 16..1 go by shuffle.  The first pass runs all 28 steps of
+//               the sizes k = 2..128 this way; afterwards every size k ends with one (steps 64..1).
+//   cross pass  up to three steps with distances j, j/2, j/4 >= 128: a thread holds the 8 slots base + a * (j/4), so all
+//               three are compare-exchanges inside the thread; consecutive threads hold consecutive slots.
+// 16 passes instead of 91 at 8192 keys.  Same comparisons as the plain network, hence the same (unique) result.
+__device__ __forceinline__ void nms_ce(unsigned long long &a, unsigned long long &b, bool desc) {
+    if ((a < b) == desc) { const unsigned long long t = a; a = b; b = t; }
+}
+// steps j_hi, j_hi/2, .., 1 (j_hi <= 64) of size k on the four keys of this lane; idx0 = slot of x[0]
+__device__ __forceinline__ void nms_chunk_steps(unsigned long long (&x)[4], int idx0, int lane, int k, int j_hi) {
+    if (j_hi >= 64) {
+        nms_ce(x[0], x[2], (idx0 & k) == 0);
+        nms_ce(x[1], x[3], ((idx0 + 32) & k) == 0);
+    }
+    if (j_hi >= 32) {
+        nms_ce(x[0], x[1], (idx0 & k) == 0);
+        nms_ce(x[2], x[3], ((idx0 + 64) & k) == 0);
+    }
+    for (int j = j_hi < 16 ? j_hi : 16; j > 0; j >>= 1) {
+        const bool lower = (lane & j) == 0;
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            const unsigned long long y = __shfl_xor_sync(0xffffffffu, x[m], j);
+            const bool desc = ((idx0 + 32 * m) & k) == 0;        // bit k of a slot and of its partner agree (k > j)
+            const bool want_max = lower == desc;                 // descending: the lower slot keeps the larger key
+            x[m] = ((x[m] > y) == want_max) ? x[m] : y;          // keys are unique (equal padding zeros: either one)
+        }
+    }
+}
+__device__ __forceinline__ void nms_bitonic_desc(unsigned long long *s, int P) {      // whole block; ends on a barrier
+    if (P < 128) { nms_bitonic_small(s, P); return; }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // ---- sizes 2..128: everything inside the 128-slot chunks
+    for (int c = warp; c < (P >> 7); c += kSortThreads / 32) {
+        const int idx0 = (c << 7) + lane;
+        unsigned long long x[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) x[m] = s[idx0 + 32 * m];
+        for (int k = 2; k <= 128; k <<= 1) nms_chunk_steps(x, idx0, lane, k, k >> 1);
+#pragma unroll
+        for (int m = 0; m < 4; ++m) s[idx0 + 32 * m] = x[m];
+    }
+    __syncthreads();
+    for (int k = 256; k <= P; k <<= 1) {
+        // ---- cross passes: distances k/2 .. 128, three steps at a time
+        int j = k >> 1;
+        while (j >= 128) {
+            int S = 1;
+            if (j >= 256) S = 2;
+            if (j >= 512) S = 3;
+            const int jl = j >> (S - 1);                           // smallest distance of this pass
+            for (int t = threadIdx.x; t < (P >> S); t += kSortThreads) {
+                const int base = ((t & ~(jl - 1)) << S) | (t & (jl - 1));
+                const bool desc = (base & k) == 0;                 // k > j: the same for all slots of the thread
+                unsigned long long x[8];
+#pragma unroll
+                for (int a = 0; a < 8; ++a)
+                    if (a < (1 << S)) x[a] = s[base + a * jl];
+#pragma unroll
+                for (int st = 2; st >= 0; --st) {
+                    if (st < S) {
+#pragma unroll
+                        for (int a = 0; a < 8; ++a)
+                            if (a < (1 << S) && !(a & (1 << st))) nms_ce(x[a], x[a | (1 << st)], desc);
+                    }
+                }
+#pragma unroll
+                for (int a = 0; a < 8; ++a)
+                    if (a < (1 << S)) s[base + a * jl] = x[a];
+            }
+            __syncthreads();
+            j >>= S;
+        }
+        // ---- distances 64..1 inside the chunks
+        for (int c = warp; c < (P >> 7); c += kSortThreads / 32) {
+            const int idx0 = (c << 7) + lane;
+            unsigned long long x[4];
+#pragma unroll
+            for (int m = 0; m < 4; ++m) x[m] = s[idx0 + 32 * m];
+            nms_chunk_steps(x, idx0, lane, k, 64);
+#pragma unroll
+            for (int m = 0; m < 4; ++m) s[idx0 + 32 * m] = x[m];
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kSortThreads)      // 50 registers; capped at 32 for two blocks per SM it spills and is no faster
 k_nms_sort(const unsigned long long *__restrict__ keys, const int *__restrict__ count, int A,
            const float4 *__restrict__ boxes, const int *__restrict__ cls, float4 *__restrict__ sbox,
            float *__restrict__ sscore, int *__restrict__ scls, int *__restrict__ sanchor) {
