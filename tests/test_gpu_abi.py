@@ -33,7 +33,9 @@ def _raw_call(lib, feats, grads, batch, nc, imgsz, out, ws, stream):
 
 
 @pytest.mark.parametrize("imgsz,B,max_gt,kw", [(128, 3, 6, {"p_tiny": 0.3, "p_nested": 0.3}), (640, 8, 20, {}),
-                                                (672, 2, 12, {})])
+                                                (672, 2, 12, {}),
+                                                # more than 1024 GT: the memset node + multi-block k_pack_gt in the graph
+                                                (320, 8, 300, {"fixed_count": 300, "dense": True})])
 def test_detection_loss_cuda_graph_capture_and_replay(cuda_lib, imgsz, B, max_gt, kw):
     """ys_detection_loss allocates nothing and never synchronises: the whole call (pack, assign, loss; programmatic
     dependent launches included) is captured into a CUDA graph and replayed; every replay gives bit-identical loss
