@@ -940,6 +940,8 @@ k_nms_suppress_grid(const int *__restrict__ count, int A, const float4 *__restri
     __shared__ float s_red[7][kWarps];
     __shared__ int s_part[kWarps];
     __shared__ int s_nlist[2];
+    constexpr int kWorkClasses = 128;
+    __shared__ int s_hist[kWorkClasses];
     const int b = blockIdx.x;
     const int n = count[b];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1050,14 +1052,25 @@ k_nms_suppress_grid(const int *__restrict__ count, int A, const float4 *__restri
     // ---- is the image sparse enough?  The scan below visits every candidate of a box's window; dense scenes (boxes jittered
     //      around a few centres, low thresholds) have hundreds of candidates per window and are better served by the tile
     //      kernel, whose cost does not depend on the density.  The window populations come from the cell table for free.
+    //      The same pass files every box under a work class (its window population + a charge per row), and round 0 then
+    //      walks the boxes in order of descending class: the 32 lanes of a warp get windows of similar size.  (Walked in
+    //      cell order, a warp's lanes had windows between a few and a few hundred candidates: ncu read 11 of 32 lanes
+    //      active per instruction.)  Results do not depend on the order the boxes of a round are visited in.
     {
+        for (int i = tid; i < kWorkClasses; i += kGridThreads) s_hist[i] = 0;
+        __syncthreads();
         long long pop = 0;
         for (int p = tid; p < n; p += kGridThreads) {
             const float4 a = s_box[p];
             const float c2x = a.x + a.z, c2y = a.y + a.w;
             const float R2x = fminf(R2xg, kown * (a.z - a.x) + slack), R2y = fminf(R2yg, kown * (a.w - a.y) + slack);
             const int cx0 = cell_x(c2x - R2x), cx1 = cell_x(c2x + R2x), cy0 = cell_y(c2y - R2y), cy1 = cell_y(c2y + R2y);
-            for (int cy = cy0; cy <= cy1; ++cy) pop += s_cell[cy * kGridDim + cx1 + 1] - s_cell[cy * kGridDim + cx0];
+            int mine = 0;
+            for (int cy = cy0; cy <= cy1; ++cy) mine += s_cell[cy * kGridDim + cx1 + 1] - s_cell[cy * kGridDim + cx0];
+            pop += mine;
+            const int wc = kWorkClasses - 1 - min((mine + 2 * (cy1 - cy0 + 1)) >> 2, kWorkClasses - 1);    // descending work
+            s_list0[p] = (unsigned short)wc;
+            atomicAdd(&s_hist[wc], 1);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) pop += __shfl_xor_sync(0xffffffffu, pop, o);
@@ -1067,6 +1080,23 @@ k_nms_suppress_grid(const int *__restrict__ count, int A, const float4 *__restri
             if (tid == 0) fallback[b] = 1;
             return;
         }
+        if (warp == 0) {                                   // exclusive prefix over the work classes
+            int run = 0;
+            for (int c0 = 0; c0 < kWorkClasses; c0 += 32) {
+                const int v = s_hist[c0 + lane];
+                int inc = v;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += t;
+                }
+                s_hist[c0 + lane] = run + inc - v;
+                run += __shfl_sync(0xffffffffu, inc, 31);
+            }
+        }
+        __syncthreads();
+        for (int p = tid; p < n; p += kGridThreads) s_list1[atomicAdd(&s_hist[s_list0[p]], 1)] = (unsigned short)p;
+        __syncthreads();
     }
     // ---- rounds.  Round 0 walks every position; later rounds only the positions still undecided (compacted lists).
     volatile unsigned short *rs = s_rs;
@@ -1076,9 +1106,9 @@ k_nms_suppress_grid(const int *__restrict__ count, int A, const float4 *__restri
         const unsigned short *lin = (rounds & 1) ? s_list0 : s_list1;        // written by the previous round
         unsigned short *lout = (rounds & 1) ? s_list1 : s_list0;
         int *nout = &s_nlist[rounds & 1 ? 1 : 0];
-        const int nin = rounds == 0 ? n : s_nlist[rounds & 1 ? 0 : 1];
+        const int nin = rounds == 0 ? n : s_nlist[rounds & 1 ? 0 : 1];      // round 0: s_list1 = all positions, heaviest first
         for (int i = tid; i < nin; i += kGridThreads) {
-            const int p = rounds == 0 ? i : (int)lin[i];
+            const int p = (int)lin[i];
             const float4 a = s_box[p];
             const unsigned ra = rs[p] & kRankMask;
             const float c2x = a.x + a.z, c2y = a.y + a.w;
@@ -1087,10 +1117,18 @@ k_nms_suppress_grid(const int *__restrict__ count, int A, const float4 *__restri
             const float area_a = area_plain(a);
             const float tw_a = fmaxf(0.99f * thr * (a.z - a.x), 0.f), th_a = fmaxf(0.99f * thr * (a.w - a.y), 0.f);
             const int cls_a = CLASS_AWARE ? (int)s_cls[p] : 0;
+            const float thr999 = 0.999f * thr;
             bool removed = false, pending = false;
-            for (int cy = cy0; cy <= cy1 && !removed; ++cy) {
-                const int q1 = s_cell[cy * kGridDim + cx1 + 1];
-                for (int q = s_cell[cy * kGridDim + cx0]; q < q1; ++q) {
+            // one flat loop over the window's rows: a lane moves on to its next row without waiting for the other lanes' rows
+            int cy = cy0, q = s_cell[cy0 * kGridDim + cx0], q1 = s_cell[cy0 * kGridDim + cx1 + 1];
+            {
+                for (;; ++q) {
+                    while (q >= q1 && cy < cy1) {
+                        ++cy;
+                        q = s_cell[cy * kGridDim + cx0];
+                        q1 = s_cell[cy * kGridDim + cx1 + 1];
+                    }
+                    if (q >= q1) break;
                     // straight-line candidate test (no early `continue`s: a warp's lanes walk different candidates, and
                     // every divergent exit was being executed by the whole warp): higher-scored, not removed, same class,
                     // and -- IoU > thr needs inter_w > thr * own width and inter_h > thr * own height (see the note above
@@ -1101,12 +1139,14 @@ k_nms_suppress_grid(const int *__restrict__ count, int A, const float4 *__restri
                     const float ih = YS_SUB(fminf2(e.w, a.w), fmaxf2(e.y, a.y));
                     bool cand = ((rq & kRankMask) < ra) & !(rq & kRemoved) & (iw > tw_a) & (ih > th_a);
                     if (CLASS_AWARE) cand = cand & ((int)s_cls[q] == cls_a);
-                    if (cand) {
-                        // iou_nms(e, a) > thr with the reference's arithmetic (train_yolo11_cuda.py:418-435, :396); the
-                        // division only when the quotient could exceed thr (den > 0; fl(x / y) <= (x / y) * (1 + 2^-24))
-                        const float inter = YS_MUL(iw, ih);
-                        const float den = YS_ADD(YS_SUB(YS_ADD(area_plain(e), area_a), inter), kEpsNms);
-                        if (inter > __fmul_rn(0.999f * thr, den) && !(YS_DIV(inter, den) <= thr)) {
+                    // iou_nms(e, a) > thr with the reference's arithmetic (train_yolo11_cuda.py:418-435, :396).  inter and den
+                    // are computed for every candidate (a warp's lanes walk different candidates: ~12 % pass the gate, so a
+                    // branch here was taken by almost every warp with a handful of lanes); the division only when the
+                    // quotient could exceed thr (den > 0; fl(x / y) <= (x / y) * (1 + 2^-24))
+                    const float inter = YS_MUL(iw, ih);
+                    const float den = YS_ADD(YS_SUB(YS_ADD(area_plain(e), area_a), inter), kEpsNms);
+                    if (cand & (inter > __fmul_rn(thr999, den))) {
+                        if (!(YS_DIV(inter, den) <= thr)) {
                             if (rq & kKept) { removed = true; break; }
                             pending = true;                                // undecided when read (it may have been decided
                         }                                                  // since: then the next round sees it)
