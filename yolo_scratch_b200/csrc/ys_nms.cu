@@ -1120,25 +1120,32 @@ k_nms_suppress_grid(const int *__restrict__ count, int A, const float4 *__restri
             const float thr999 = 0.999f * thr;
             bool removed = false, pending = false;
             // one flat loop over the window's rows: a lane moves on to its next row without waiting for the other lanes' rows
+            // (the step to the next row is predicated, not a branch: with ~10 candidates per row some lane of the warp changes
+            // rows in almost every trip; an empty row costs its lane one idle trip.  Loading the next trip's candidate under
+            // this trip's arithmetic -- software pipelining -- was measured: +17 % instructions, 764 -> 796 us, not taken)
             int cy = cy0, q = s_cell[cy0 * kGridDim + cx0], q1 = s_cell[cy0 * kGridDim + cx1 + 1];
             {
-                for (;; ++q) {
-                    while (q >= q1 && cy < cy1) {
-                        ++cy;
-                        q = s_cell[cy * kGridDim + cx0];
-                        q1 = s_cell[cy * kGridDim + cx1 + 1];
-                    }
-                    if (q >= q1) break;
+                for (;;) {
+                    const bool adv = q >= q1;
+                    if (adv && cy >= cy1) break;
+                    cy += adv ? 1 : 0;
+                    const int cb = cy * kGridDim;
+                    const int nq = s_cell[cb + cx0], nq1 = s_cell[cb + cx1 + 1];
+                    q = adv ? nq : q;
+                    q1 = adv ? nq1 : q1;
+                    const bool valid = q < q1;
+                    const int qq = q;
+                    q += valid ? 1 : 0;
                     // straight-line candidate test (no early `continue`s: a warp's lanes walk different candidates, and
                     // every divergent exit was being executed by the whole warp): higher-scored, not removed, same class,
                     // and -- IoU > thr needs inter_w > thr * own width and inter_h > thr * own height (see the note above
                     // the kernel; 1 % of slack for the reference's fp32 rounding) -- two compares that settle almost every pair
-                    const unsigned rq = rs[q];
-                    const float4 e = s_box[q];
+                    const unsigned rq = rs[qq];                  // qq <= n: an idle trip reads inside the shared arrays, its result is masked
+                    const float4 e = s_box[qq];
                     const float iw = YS_SUB(fminf2(e.z, a.z), fmaxf2(e.x, a.x));
                     const float ih = YS_SUB(fminf2(e.w, a.w), fmaxf2(e.y, a.y));
-                    bool cand = ((rq & kRankMask) < ra) & !(rq & kRemoved) & (iw > tw_a) & (ih > th_a);
-                    if (CLASS_AWARE) cand = cand & ((int)s_cls[q] == cls_a);
+                    bool cand = valid & ((rq & kRankMask) < ra) & !(rq & kRemoved) & (iw > tw_a) & (ih > th_a);
+                    if (CLASS_AWARE) cand = cand & ((int)s_cls[qq] == cls_a);
                     // iou_nms(e, a) > thr with the reference's arithmetic (train_yolo11_cuda.py:418-435, :396).  inter and den
                     // are computed for every candidate (a warp's lanes walk different candidates: ~12 % pass the gate, so a
                     // branch here was taken by almost every warp with a handful of lanes); the division only when the
