@@ -39,11 +39,18 @@ __global__ void __launch_bounds__(kBlThreads) k_bbox_loss(BboxLossArgs P) {
     const bool in = row < P.n;
     const bool fg = in && P.fg_mask[row] != 0;
     const float inv_tss = 1.0f / P.tss[0];
+    // R == 16 with 16-byte aligned tensors (the YOLO head): a lane's 16 bins are four 16-byte words
+    const bool vec = R == 16 && ((reinterpret_cast<uintptr_t>(P.pred_dist) | reinterpret_cast<uintptr_t>(P.grad_dist)) & 15) == 0;
     if (in && !fg) {
         if (P.grad_boxes && side == 0) P.grad_boxes[row] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (P.grad_dist) {
             float *g = P.grad_dist + ((size_t)row * 4 + side) * R;
-            for (int j = 0; j < R; ++j) g[j] = 0.f;
+            if (vec) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) reinterpret_cast<float4 *>(g)[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            } else {
+                for (int j = 0; j < R; ++j) g[j] = 0.f;
+            }
         }
     }
     // weight = target_scores.sum(-1)[fg_mask]  (:297); the four lanes of the row split the classes, fixed order
@@ -75,6 +82,40 @@ __global__ void __launch_bounds__(kBlThreads) k_bbox_loss(BboxLossArgs P) {
             const int tl = (int)tt;
             const float wl = (float)(tl + 1) - tt, wr = 1.0f - wl;
             const float *z = P.pred_dist + ((size_t)row * 4 + side) * R;
+            if (vec) {
+                float zz[16];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float4 q = reinterpret_cast<const float4 *>(z)[j];
+                    zz[4 * j] = q.x; zz[4 * j + 1] = q.y; zz[4 * j + 2] = q.z; zz[4 * j + 3] = q.w;
+                }
+                float m = zz[0];
+#pragma unroll
+                for (int j = 1; j < 16; ++j) m = fmaxf(m, zz[j]);
+                float s = 0.f, ztl = 0.f, ztr = 0.f;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    zz[j] = expf(zz[j] - m);                 // same operations, same order as the scalar path below
+                    s += zz[j];
+                }
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {               // z[tl], z[tl + 1] back from exp: read them again instead
+                    ztl = j == tl ? z[j] : ztl;
+                    ztr = j == tl + 1 ? z[j] : ztr;
+                }
+                const float lse = m + logf(s);
+                const float ce = (lse - ztl) * wl + (lse - ztr) * wr;
+                acc_dfl = ce * 0.25f * w;
+                if (P.grad_dist) {
+                    float *g = P.grad_dist + ((size_t)row * 4 + side) * R;
+                    const float k = 0.25f * w * inv_tss, inv_s = 1.0f / s;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) zz[j] = k * (zz[j] * inv_s - (j == tl ? wl : 0.f) - (j == tl + 1 ? wr : 0.f));
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        reinterpret_cast<float4 *>(g)[j] = make_float4(zz[4 * j], zz[4 * j + 1], zz[4 * j + 2], zz[4 * j + 3]);
+                }
+            } else {
             float m = z[0];
             for (int j = 1; j < R; ++j) m = fmaxf(m, z[j]);
             float s = 0.f;
@@ -90,6 +131,7 @@ __global__ void __launch_bounds__(kBlThreads) k_bbox_loss(BboxLossArgs P) {
                     const float p = expf(z[j] - m) * inv_s;
                     g[j] = k * (p - (j == tl ? wl : 0.f) - (j == tl + 1 ? wr : 0.f));
                 }
+            }
             }
         } else if (P.grad_dist) {
             P.grad_dist[(size_t)row * 4 + side] = 0.f;
