@@ -43,17 +43,19 @@ def calculate_ap(tp, fp, n_gt):
     import numpy as np
     if n_gt == 0:
         return 0.0
-    dets = sorted([(float(s), 1) for s in tp] + [(float(s), 0) for s in fp], key=lambda d: d[0], reverse=True)
-    if not dets:
+    tp = np.asarray(tp, dtype=np.float64).reshape(-1)
+    fp = np.asarray(fp, dtype=np.float64).reshape(-1)
+    if tp.size + fp.size == 0:
         return 0.0
-    flags = np.array([d[1] for d in dets])
+    # the reference's `sorted(tp + fp, reverse=True)` is stable: equal scores keep the listed order, true positives first
+    order = np.argsort(-np.concatenate([tp, fp]), kind="stable")
+    flags = np.concatenate([np.ones(tp.size, dtype=np.int64), np.zeros(fp.size, dtype=np.int64)])[order]
     ctp, cfp = np.cumsum(flags), np.cumsum(1 - flags)
     prec = ctp / (ctp + cfp + 1e-6)
     rec = ctp / n_gt
     mrec = np.concatenate([[0.0], rec, [1.0]])
     mpre = np.concatenate([[0.0], prec, [0.0]])
-    for k in range(len(mpre) - 1, 0, -1):
-        mpre[k - 1] = np.maximum(mpre[k - 1], mpre[k])
+    mpre = np.maximum.accumulate(mpre[::-1])[::-1]          # the precision envelope (:311-313), without the Python loop
     idx = np.where(mrec[1:] != mrec[:-1])[0]
     return np.sum((mrec[idx + 1] - mrec[idx]) * mpre[idx + 1])
 
@@ -75,12 +77,13 @@ def match_detections(predictions, targets, conf_threshold, iou_thresholds):
     pb = torch.zeros(B, P, 4, device=dev)
     ps = torch.full((B, P), float("-inf"), device=dev)
     pc = torch.zeros(B, dtype=torch.int32, device=dev)
-    for i, p in enumerate(predictions):
-        n = int(p["boxes"].shape[0])
-        if n:
-            pb[i, :n] = p["boxes"].to(dev, torch.float32)
-            ps[i, :n] = p["scores"].to(dev, torch.float32)
-            pc[i] = n
+    pcounts = [int(p["boxes"].shape[0]) for p in predictions]
+    if sum(pcounts):                                            # one scatter for the whole batch instead of three ops per image
+        rows = torch.repeat_interleave(torch.arange(B), torch.tensor(pcounts)).to(dev)
+        cols = torch.cat([torch.arange(n) for n in pcounts]).to(dev)
+        pb[rows, cols] = torch.cat([p["boxes"].to(dev, torch.float32).view(-1, 4) for p in predictions], 0)
+        ps[rows, cols] = torch.cat([p["scores"].to(dev, torch.float32).view(-1) for p in predictions], 0)
+    pc = torch.tensor(pcounts, dtype=torch.int32, device=dev)
     ps, order = torch.sort(ps, dim=1, descending=True, stable=True)            # :170 (scores are unique in practice)
     pb = torch.gather(pb, 1, order.unsqueeze(-1).expand(-1, -1, 4)).contiguous()
     counts = [int(t["boxes"].shape[0]) for t in targets]
@@ -111,14 +114,12 @@ def evaluate_detections(predictions, targets, conf_threshold=0.25, iou_threshold
         return {"precision": 0.0, "recall": 0.0, "mAP50": 0.0, "mAP50-95": 0.0 if len(ladder) == 0 else float(np.mean([0.0] * len(ladder)))}
     tp, scores, nv, n_gt = match_detections(predictions, targets, conf_threshold, thresholds)
     aps = []
+    valid = np.arange(tp.shape[1])[None, :] < nv[:, None]                    # (B, P): detections above the confidence cut
     for t in range(len(ladder)):
-        tps, fps = [], []
-        for b in range(tp.shape[0]):
-            s, f = scores[b, :nv[b]], tp[b, :nv[b], t].astype(bool)
-            tps.extend(s[f].tolist())
-            fps.extend(s[~f].tolist())
-        aps.append(calculate_ap(tps, fps, n_gt))
-    n_tp = int(sum(tp[b, :nv[b], -1].sum() for b in range(tp.shape[0])))
+        f = tp[:, :, t].astype(bool)
+        # row-major masks: image by image, score-descending inside an image -- the order the reference lists them in
+        aps.append(calculate_ap(scores[valid & f], scores[valid & ~f], n_gt))
+    n_tp = int(tp[:, :, -1][valid].sum())
     n_det = int(nv.sum())
     precision = n_tp / n_det if n_det > 0 else 0.0
     recall = n_tp / n_gt if n_gt > 0 else 0.0
