@@ -501,10 +501,19 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
     const float area_p = area_eps_h(p.x, p.y, p.z, p.w);
     // bounding box of this warp's anchor centres (non-live lanes neutral); order-preserving float <-> uint map so
     // that the dense entry point may be given any (also negative) anchor points
-    const float wx_min = ord_to_float(__reduce_min_sync(0xffffffffu, live ? float_to_ord(ax) : 0xffffffffu));
-    const float wx_max = ord_to_float(__reduce_max_sync(0xffffffffu, live ? float_to_ord(ax) : 0u));
-    const float wy_min = ord_to_float(__reduce_min_sync(0xffffffffu, live ? float_to_ord(ay) : 0xffffffffu));
-    const float wy_max = ord_to_float(__reduce_max_sync(0xffffffffu, live ? float_to_ord(ay) : 0u));
+    // (fused: the centres are positive, and positive floats order like their bit patterns -- no mapping needed)
+    float wx_min, wx_max, wy_min, wy_max;
+    if (FUSED) {
+        wx_min = __uint_as_float(__reduce_min_sync(0xffffffffu, live ? __float_as_uint(ax) : 0x7f800000u));
+        wx_max = __uint_as_float(__reduce_max_sync(0xffffffffu, live ? __float_as_uint(ax) : 0u));
+        wy_min = __uint_as_float(__reduce_min_sync(0xffffffffu, live ? __float_as_uint(ay) : 0x7f800000u));
+        wy_max = __uint_as_float(__reduce_max_sync(0xffffffffu, live ? __float_as_uint(ay) : 0u));
+    } else {
+        wx_min = ord_to_float(__reduce_min_sync(0xffffffffu, live ? float_to_ord(ax) : 0xffffffffu));
+        wx_max = ord_to_float(__reduce_max_sync(0xffffffffu, live ? float_to_ord(ax) : 0u));
+        wy_min = ord_to_float(__reduce_min_sync(0xffffffffu, live ? float_to_ord(ay) : 0xffffffffu));
+        wy_max = ord_to_float(__reduce_max_sync(0xffffffffu, live ? float_to_ord(ay) : 0u));
+    }
 
     int cnt = 0, first = -1, best_g = 0;
     float best_ov = -1.f;
@@ -550,8 +559,9 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
         // around the centres whenever the predicted sides are shorter than 15.5 cells (always, in practice).
         const float rx0 = ord_to_float(__reduce_min_sync(0xffffffffu, live ? float_to_ord(p.x) : 0xffffffffu));
         const float ry0 = ord_to_float(__reduce_min_sync(0xffffffffu, live ? float_to_ord(p.y) : 0xffffffffu));
-        const float rx1 = ord_to_float(__reduce_max_sync(0xffffffffu, live ? float_to_ord(p.z) : 0u));
-        const float ry1 = ord_to_float(__reduce_max_sync(0xffffffffu, live ? float_to_ord(p.w) : 0u));
+        // x2 = (gx + d) * stride > 0 and likewise y2: bit patterns order like the values; x1 / y1 may be negative
+        const float rx1 = __uint_as_float(__reduce_max_sync(0xffffffffu, live ? __float_as_uint(p.z) : 0u));
+        const float ry1 = __uint_as_float(__reduce_max_sync(0xffffffffu, live ? __float_as_uint(p.w) : 0u));
 #endif
         const bool warp_live = __any_sync(0xffffffffu, live);
         for (int t = 0; t < ntiles; ++t) {
