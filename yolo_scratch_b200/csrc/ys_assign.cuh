@@ -589,7 +589,9 @@ k_assign(LevelSet L, AssignIO io, int B, const __grid_constant__ ScanMaps M) {
                         if (ovr > best_ov) { best_ov = ovr; best_g = t0 + j; }    // first maximum (ascending j)
                         const unsigned bits = __float_as_uint(ovr);
                         const unsigned mx = __reduce_max_sync(0xffffffffu, bits);
-                        if (mx != 0u) {
+                        // the block's key for this GT only grows: a warp whose best IoU is below the key's IoU word (a
+                        // possibly stale read -- then the atomic below settles it) cannot change it
+                        if (mx != 0u && mx >= reinterpret_cast<volatile unsigned *>(&S.rkey[j])[1]) {
                             const unsigned who = __ballot_sync(0xffffffffu, bits == mx);
                             if (lane == __ffs(who) - 1) atomicMax(&S.rkey[j], argmax_key(ovr, (unsigned)a));
                         }
