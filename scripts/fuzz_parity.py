@@ -1,8 +1,9 @@
 #!/usr/bin/env python
 """Randomised parity sweep on the GPU box (not part of the test suite): random head shapes, class counts, batch sizes and
 GT densities through the fused loss (spliced-oracle check of tests/test_gpu_loss.py: decoded boxes, bit-exact indices,
-items, gradients), random candidate sets through the batched NMS (keep lists vs the C oracle) and random heads through the
-inference decode (both layouts vs the oracle port).
+items, gradients), random candidate sets through the batched NMS (keep lists vs the C oracle), random heads through the
+inference decode (both layouts vs the oracle port) and random dense inputs through TaskAlignedAssigner (default, use_topk and
+ciou_assign modes vs the oracle port: indices bit-exact).
     python scripts/fuzz_parity.py [--seed 0] [--loss 40] [--nms 40] [--decode 30]"""
 import argparse
 import json
@@ -27,13 +28,14 @@ def main():
     ap.add_argument("--loss", type=int, default=40)
     ap.add_argument("--nms", type=int, default=40)
     ap.add_argument("--decode", type=int, default=30)
+    ap.add_argument("--assign", type=int, default=30)
     a = ap.parse_args()
     rng = random.Random(a.seed)
     import test_gpu_loss as tl
     from oracle import c_oracle, ref_port as orc
     from yolo_scratch_b200.head_decode import detect_inference
     from yolo_scratch_b200.train_yolo11_cuda import nms_batched
-    out = {"seed": a.seed, "loss": [], "nms": [], "decode": []}
+    out = {"seed": a.seed, "loss": [], "nms": [], "decode": [], "assign": []}
     t0 = time.time()
     for k in range(a.loss):
         h0 = rng.choice([4, 8, 9, 12, 13, 16, 20, 21, 28, 40])           # P3 side; P4 = ceil/2, P5 = ceil/4 (odd sizes included)
@@ -106,6 +108,31 @@ def main():
             case["ok"] = False
             case["error"] = repr(ex)[:300]
         out["decode"].append(case)
+    import test_gpu_assign as ta
+    from yolo_scratch_b200.losses import TaskAlignedAssigner
+    for k in range(a.assign):
+        h0 = rng.choice([4, 8, 12, 20, 40])
+        shapes = ((h0, h0), ((h0 + 1) // 2, (h0 + 1) // 2), ((h0 + 3) // 4, (h0 + 3) // 4))
+        nc = rng.choice([1, 3, 8, 20, 80])
+        B = rng.randint(1, 4)
+        max_gt = rng.choice([1, 4, 20, 60, 130])
+        topk = rng.choice([0, 0, 5, 13])
+        ciou = rng.random() < 0.3
+        kw = {"p_empty": rng.choice([0.0, 0.3]), "p_tiny": rng.choice([0.0, 0.3]), "p_nested": rng.choice([0.0, 0.3])}
+        seed = 40_000 + 7 * k + a.seed * 1000
+        case = {"shapes": shapes, "nc": nc, "B": B, "max_gt": max_gt, "topk": topk, "ciou": ciou, "kw": kw, "seed": seed}
+        try:
+            inp = synth.make_assigner_inputs(B, shapes, synth.LEVEL_STRIDES, nc, max_gt, seed, **kw)
+            asg = TaskAlignedAssigner(topk=topk or 50, num_classes=nc, alpha=0.5, beta=4.0, use_topk=topk > 0, ciou_assign=ciou)
+            got = [o.cpu() for o in asg.forward(*[x.cuda() for x in inp])]
+            ref = orc.assign(*inp, nc, 0.5, 4.0, ciou_assign=ciou, topk=topk)
+            if inp[3].shape[1] > 0:
+                ta._check(got, ref)
+            case["ok"] = True
+        except Exception as ex:
+            case["ok"] = False
+            case["error"] = repr(ex)[:300]
+        out["assign"].append(case)
     torch.cuda.synchronize()
     summary = {k: {"cases": len(v), "failed": sum(1 for c in v if not c["ok"])} for k, v in out.items() if isinstance(v, list)}
     out["summary"] = summary
