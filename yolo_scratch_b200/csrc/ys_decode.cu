@@ -237,21 +237,34 @@ __global__ void __launch_bounds__(kDecThreads) k_decode_infer_am(LevelSet L, int
     }
 }
 
+// One thread = one row i and four consecutive columns j (a 16-byte store when the row pitch allows it).
 __global__ void k_pairwise_iou(const float4 *__restrict__ b1, int N, const float4 *__restrict__ b2, int M, int kind,
                                float *__restrict__ out) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     const int i = blockIdx.y;
-    if (j >= M || i >= N) return;
-    const float4 p = b1[i], q = b2[j];
-    float v;
-    if (kind == 0) v = iou_nms(p, area_plain(p), q, area_plain(q));
-    else {
-        // bbox_iou(xywh=False) without the assigner's clamp (losses/yolo_v8_loss.py:31-44)
-        const float inter = inter_area(p.x, p.y, p.z, p.w, q.x, q.y, q.z, q.w);
-        const float uni = YS_ADD(YS_SUB(YS_ADD(area_eps_h(p.x, p.y, p.z, p.w), area_eps_h(q.x, q.y, q.z, q.w)), inter), kEpsIou);
-        v = YS_DIV(inter, uni);
+    if (j0 >= M || i >= N) return;
+    const float4 p = b1[i];
+    const float area_p = kind == 0 ? area_plain(p) : area_eps_h(p.x, p.y, p.z, p.w);
+    float v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const float4 q = b2[min(j0 + u, M - 1)];
+        if (kind == 0) v[u] = iou_nms(p, area_p, q, area_plain(q));
+        else {
+            // bbox_iou(xywh=False) without the assigner's clamp (losses/yolo_v8_loss.py:31-44)
+            const float inter = inter_area(p.x, p.y, p.z, p.w, q.x, q.y, q.z, q.w);
+            const float uni = YS_ADD(YS_SUB(YS_ADD(area_p, area_eps_h(q.x, q.y, q.z, q.w)), inter), kEpsIou);
+            v[u] = YS_DIV(inter, uni);
+        }
     }
-    out[(size_t)i * M + j] = v;
+    float *row = out + (size_t)i * M + j0;
+    if (j0 + 3 < M && (reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+        *reinterpret_cast<float4 *>(row) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (j0 + u < M) row[u] = v[u];
+    }
 }
 
 // Elementwise bbox_iou, all modes (losses/yolo_v8_loss.py:12-61), op order as the reference.
@@ -379,7 +392,7 @@ extern "C" int ys_pairwise_iou(const float *boxes1, int N, const float *boxes2, 
     YS_REQUIRE((((uintptr_t)boxes1 | (uintptr_t)boxes2) & 15) == 0, YS_ERR_BAD_ARG, "box pointers must be 16-byte aligned");
     YS_REQUIRE(kind == 0 || kind == 1, YS_ERR_BAD_ARG, "kind must be 0 or 1");
     YS_REQUIRE(N <= 65535, YS_ERR_UNSUPPORTED, "N must be <= 65535");
-    dim3 grid((M + 255) / 256, N);
+    dim3 grid((M + 1023) / 1024, N);
     k_pairwise_iou<<<grid, 256, 0, (cudaStream_t)stream_v>>>((const float4 *)boxes1, N, (const float4 *)boxes2, M, kind, out);
     YS_CHECK_LAUNCH("k_pairwise_iou");
     return YS_OK;
